@@ -1,0 +1,211 @@
+/*
+ * taxi_xf.h -- C ABI of libtaxi_xf.so: the B200 (sm_100a) analyze+transform kernels behind
+ * `preprocessing_fn` of the Chicago-taxi TFX pipeline.
+ *
+ * The reference (pablomendes/kubeflow-tfx-workshop) has no FFI of its own: the hot path is the
+ * Python callback airflow-dags/taxi_utils.py:106-145, whose arithmetic runs inside
+ * tensorflow-transform / TensorFlow / Beam.  Each entry point below therefore cites the
+ * reference CALL SITE (file:line under /root/reference) whose behaviour it replaces.
+ *
+ * Conventions
+ *  - every function returns 0 (TXF_OK) or a negative TXF_ERR_*; txf_last_error() returns the
+ *    message of the calling thread's last failure;
+ *  - plain pointers and sizes only.  Pointers named *_dev / marked "device" are CUDA device
+ *    addresses owned by the caller (e.g. torch tensors' data_ptr()); nothing here allocates or
+ *    frees device memory, and nothing synchronises the stream unless its name ends in _sync;
+ *  - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
+ *  - a chunk of rows is at most 2^31-1 rows, string pools at most 2^31-1 bytes (int32
+ *    offsets, Arrow layout).  Larger shards are fed chunk by chunk; analyzer state accumulates;
+ *  - numeric values pointers must be 16-byte aligned; validity is an Arrow bitmap (LSB first,
+ *    1 = present) or NULL when every row is present; string pools must be readable for
+ *    TXF_POOL_SLACK bytes past their last byte.
+ */
+#ifndef TAXI_XF_H_
+#define TAXI_XF_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TXF_ABI_VERSION 1
+#define TXF_MAX_COLS 16   /* columns handled by one analyzer launch */
+#define TXF_MAX_OPS 32    /* column ops in one fused transform program */
+#define TXF_POOL_SLACK 16 /* readable bytes required past the end of a string pool */
+#define TXF_QMAX_TARGETS 64 /* bracket-count fast path: at most this many boundaries */
+
+enum { TXF_OK = 0, TXF_ERR_ARG = -1, TXF_ERR_CUDA = -2, TXF_ERR_CAPACITY = -3 };
+enum { TXF_F32 = 0, TXF_I64 = 1 };
+
+typedef void* txf_stream_t;
+
+#if defined(__GNUC__)
+#define TXF_API __attribute__((visibility("default")))
+#else
+#define TXF_API
+#endif
+
+TXF_API const char* txf_last_error(void);
+TXF_API int txf_abi_version(void);
+
+/* ------------------------------------------------------------------------------------------
+ * Moments analyzer  -- tft.scale_to_z_score's mean/variance combiner
+ * (taxi_utils.py:116-119).  State per column: double[3] = (count, mean, M2) over the
+ * zero-filled column (_fill_in_missing, taxi_utils.py:86-103); int64 cells are rounded to fp32
+ * first, as tft does.
+ * ------------------------------------------------------------------------------------------ */
+TXF_API size_t txf_moments_workspace_bytes(int ncols);
+/* accumulate one chunk into state_dev[ncols*3] (zero-initialised by the caller) */
+TXF_API int txf_moments_update(const void* const* values, const uint8_t* const* valid, const int32_t* dtype,
+                       int ncols, int64_t n, double* state_dev, void* workspace_dev, txf_stream_t stream);
+/* Chan-merge nstates states laid out [nstates][ncols][3] in index order (rank order) */
+TXF_API int txf_moments_merge(const double* states_dev, int nstates, int ncols, double* state_out_dev,
+                      txf_stream_t stream);
+/* state -> float[ncols*2] = (mean_f32, population variance_f32) */
+TXF_API int txf_moments_finalize(const double* state_dev, int ncols, float* mean_var_dev, txf_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Exact multi-rank selection on 4-byte keys (radix select, 4 passes x 8 bits).  The general
+ * engine behind tft.bucketize's quantile analyzer (taxi_utils.py:128-130) and behind the
+ * count cut-off of the vocabulary top-k (taxi_utils.py:123-126).  Histograms are plain integer
+ * sums, so shards/ranks merge by addition (all-reduce) between _hist and _resolve.
+ *
+ * state layout (bytes): u64 hist[ncols][R][256] first (txf_msel_hist_bytes), then private.
+ * kind: 0 = numeric column cells (zero-fill, ->fp32, order key); 1 = raw uint32 keys.
+ * ranks are 1-based positions in ascending order, ascending per column; 0 = inactive entry.
+ * ------------------------------------------------------------------------------------------ */
+TXF_API size_t txf_msel_state_bytes(int ncols, int R);
+TXF_API size_t txf_msel_hist_bytes(int ncols, int R);
+TXF_API int txf_msel_begin(void* state_dev, int ncols, int R, const uint64_t* ranks_dev, txf_stream_t stream);
+/* n_dev (device, per column) overrides n when non-NULL; n then only bounds the grid */
+TXF_API int txf_msel_hist(void* state_dev, int ncols, int R, int pass, const void* const* data,
+                  const uint8_t* const* valid, const int32_t* dtype, int kind, int64_t n,
+                  const uint64_t* n_dev, txf_stream_t stream);
+TXF_API int txf_msel_resolve(void* state_dev, int ncols, int R, int pass, txf_stream_t stream);
+/* after pass 3: keys_out_dev[ncols*R] = selected keys (inactive entries -> 0) */
+TXF_API int txf_msel_result(const void* state_dev, int ncols, int R, uint32_t* keys_out_dev, txf_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Quantile boundaries, single-pass fast path (tft.bucketize analyzer, taxi_utils.py:128-130):
+ * sample -> brackets (via txf_msel_* on the sample) -> ONE counting pass over the column ->
+ * exact order statistics from the few cells that straddle each target rank.
+ * ------------------------------------------------------------------------------------------ */
+/* gather M stratified sample keys per column: sample_dev[ncols][M] */
+TXF_API int txf_qsample(const void* const* values, const uint8_t* const* valid, const int32_t* dtype, int ncols,
+                int64_t n, int64_t M, uint64_t seed, uint32_t* sample_dev, txf_stream_t stream);
+/* edges_dev[ncols][2T] ascending keys (lo0,hi0,lo1,hi1,...).  Accumulates
+ * cells_dev[ncols][4T+1] (u64; cell 2p = strictly between edge p-1 and p, cell 2p+1 = equal to
+ * edge p) and appends keys strictly inside a bracket to cand_dev[ncols][cand_cap]
+ * (cand_count_dev[ncols], u64, keeps counting past cand_cap so overflow is detectable). */
+TXF_API int txf_qcount(const void* const* values, const uint8_t* const* valid, const int32_t* dtype, int ncols,
+               int64_t n, int T, const uint32_t* edges_dev, uint64_t* cells_dev, uint32_t* cand_dev,
+               uint64_t* cand_count_dev, int64_t cand_cap, txf_stream_t stream);
+/* per target: answer directly (direct_key, cand_rank = 0) or give its 1-based rank inside the
+ * column's candidate set; status_dev[col] != 0 when a target fell outside its bracket or the
+ * candidate buffer overflowed (caller then uses the general txf_msel_* path on the column) */
+TXF_API int txf_qresolve(const uint64_t* cells_dev, const uint32_t* edges_dev, const uint64_t* cand_count_dev,
+                 int64_t cand_cap, const uint64_t* target_ranks_dev, int ncols, int T,
+                 uint32_t* direct_key_dev, uint64_t* cand_rank_dev, int32_t* status_dev,
+                 txf_stream_t stream);
+/* keys (direct where cand_rank == 0, else selected) -> distinct fp32 boundaries
+ * boundaries_dev[ncols][T], nbound_dev[ncols] */
+TXF_API int txf_qfinal(const uint32_t* direct_key_dev, const uint64_t* cand_rank_dev, const uint32_t* selected_key_dev,
+               int ncols, int T, float* boundaries_dev, int32_t* nbound_dev, txf_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Vocabulary analyzer -- tft.compute_and_apply_vocabulary(top_k, num_oov_buckets)
+ * (taxi_utils.py:121-126): exact occurrence counts in an open-addressing table keyed by
+ * (Fingerprint64, tag), first-seen bytes kept in an arena, then the top_k terms by
+ * (count, bytes) descending.
+ *
+ * table: capacity (power of two) slots of 32 bytes {u64 fp, u64 tag, u64 count, u64 strref};
+ * ctrl_dev: u64[8] = {arena_used, slots_used, overflow, kept, total, sel, 0, 0}.
+ * Both must be zero-initialised by the caller before the first count.
+ * ------------------------------------------------------------------------------------------ */
+TXF_API size_t txf_vocab_table_bytes(int64_t capacity);
+TXF_API int txf_vocab_count(const int32_t* offsets_dev, const uint8_t* pool_dev, const uint8_t* valid_dev, int64_t n,
+                    void* table_dev, int64_t capacity, uint8_t* arena_dev, int64_t arena_cap,
+                    uint64_t* ctrl_dev, txf_stream_t stream);
+/* dense list of occupied slots: ent_dev[capacity] (u32 slot ids), ctrl[4] = total distinct.
+ * Terms tft never admits ('' and anything containing \n or \r) are listed last and not
+ * counted in ctrl[3] = kept; counts_dev[i] = count of ent_dev[i] saturated to u32. */
+TXF_API int txf_vocab_compact(const void* table_dev, int64_t capacity, const uint8_t* arena_dev, uint32_t* ent_dev,
+                      uint32_t* counts_dev, uint64_t* ctrl_dev, txf_stream_t stream);
+/* serialise m listed entries for exchange between ranks: fp/tag/count/len arrays, then (after
+ * the caller turned len into exclusive offsets) the packed bytes */
+TXF_API int txf_vocab_export_meta(const void* table_dev, const uint32_t* ent_dev, int64_t m, uint64_t* fp_dev,
+                          uint64_t* tag_dev, uint64_t* count_dev, int32_t* len_dev, txf_stream_t stream);
+TXF_API int txf_vocab_export_bytes(const void* table_dev, const uint8_t* arena_dev, const uint32_t* ent_dev, int64_t m,
+                           const int64_t* out_offsets_dev, uint8_t* out_pool_dev, txf_stream_t stream);
+/* add m serialised entries (another rank's export) into a table */
+TXF_API int txf_vocab_insert(const uint64_t* fp_dev, const uint64_t* tag_dev, const uint64_t* count_dev,
+                     const int64_t* offsets_dev, const uint8_t* pool_dev, int64_t m, void* table_dev,
+                     int64_t capacity, uint8_t* arena_dev, int64_t arena_cap, uint64_t* ctrl_dev,
+                     txf_stream_t stream);
+/* keep entries with count >= *threshold_key_dev: ent_out_dev, ctrl[5] = how many */
+TXF_API int txf_vocab_filter_ge(const uint32_t* ent_dev, const uint32_t* counts_dev, int64_t m,
+                        const uint32_t* threshold_key_dev, uint32_t* ent_out_dev, uint64_t* ctrl_dev,
+                        txf_stream_t stream);
+/* sort m entries by (count, bytes) descending, in place (scratch: u32[next_pow2(m)]) */
+TXF_API size_t txf_vocab_sort_scratch_bytes(int64_t m);
+TXF_API int txf_vocab_sort(const void* table_dev, const uint8_t* arena_dev, uint32_t* ent_dev, int64_t m,
+                   void* scratch_dev, txf_stream_t stream);
+/* first k sorted entries -> id lookup table (lookup_cap slots of 16 bytes, power of two,
+ * >= 2k); the vocabulary's bytes in id order come from txf_vocab_export_* on the same list */
+TXF_API size_t txf_vocab_lookup_bytes(int64_t lookup_cap);
+TXF_API int txf_vocab_build_lookup(const void* table_dev, const uint32_t* ent_sorted_dev, int64_t k, void* lookup_dev,
+                           int64_t lookup_cap, txf_stream_t stream);
+/* lookup table from an explicit vocabulary (saved transform state; tft.apply_vocabulary) */
+TXF_API int txf_vocab_lookup_from_terms(const int32_t* voc_offsets_dev, const uint8_t* voc_pool_dev, int64_t k,
+                                void* lookup_dev, int64_t lookup_cap, txf_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Fused transform -- the per-row phase of preprocessing_fn (taxi_utils.py:115-145): one
+ * kernel runs a program of column ops over row tiles.
+ * ------------------------------------------------------------------------------------------ */
+enum {
+  TXF_OP_ZSCORE = 0,     /* :116-119  out f32 = (f32(fill(x)) - mean) / sqrt(var); p0 = float[2] {mean,var} */
+  TXF_OP_VOCAB = 1,      /* :121-126  in0 = int32 offsets, pool; p0 = lookup table, a0 = lookup_cap,
+                                       a1 = vocab size, a2 = num_oov_buckets, a3 = default_value; out i64 */
+  TXF_OP_BUCKETIZE = 2,  /* :128-130  p0 = float boundaries, p1 = int32* count (device); out i64 */
+  TXF_OP_FILL_I64 = 3,   /* :132-133  out i64 = fill(x) */
+  TXF_OP_FILL_F32 = 4,   /* :132-133  out f32 = fill(x) */
+  TXF_OP_FILL_STR = 5,   /* :132-133  out int32 offsets rebased to 0 (bytes are copied by the caller) */
+  TXF_OP_RATIO_LABEL = 6 /* :135-143  out i64 = isnan(in0) ? 0 : (in1 > in0 * f0); in0 = fare, in1 = tips */
+};
+
+typedef struct txf_op {
+  int32_t kind;
+  int32_t in_dtype; /* TXF_F32 / TXF_I64 where the op accepts both */
+  const void* in0;
+  const uint8_t* valid0;
+  const void* in1;
+  const uint8_t* valid1;
+  const uint8_t* pool;
+  void* out;
+  const void* p0;
+  const void* p1;
+  int64_t a0, a1, a2, a3;
+  float f0;
+  int32_t reserved;
+} txf_op;
+
+TXF_API int txf_transform(const txf_op* ops, int nops, int64_t n, txf_stream_t stream);
+/* name of the transform kernel and launch geometry of the last call (for profiling notes) */
+TXF_API int txf_transform_launch_info(int* grid, int* block, int* smem_bytes);
+
+/* ------------------------------------------------------------------------------------------
+ * Test hook: Fingerprint64 of every string of a column (TF StringToHashBucketFast's hash).
+ * ------------------------------------------------------------------------------------------ */
+TXF_API int txf_fingerprint64_batch(const int32_t* offsets_dev, const uint8_t* pool_dev, int64_t n, uint64_t* out_dev,
+                            txf_stream_t stream);
+
+/* number of kernels launched by this library in the calling process (bench.py gpu_launches) */
+TXF_API int64_t txf_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TAXI_XF_H_ */

@@ -1,0 +1,119 @@
+"""ctypes binding of libtaxi_xf.so (include/taxi_xf.h).
+
+There is deliberately no fallback: if the CUDA library is missing or fails to load, importing
+this module raises, and every compute entry point of the package fails with it.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import POINTER, Structure, c_char_p, c_float, c_int, c_int32, c_int64, c_size_t, c_uint64, c_void_p
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libtaxi_xf.so")
+
+TXF_MAX_COLS = 16
+TXF_MAX_OPS = 32
+TXF_POOL_SLACK = 16
+TXF_QMAX_TARGETS = 64
+TXF_F32, TXF_I64 = 0, 1
+(OP_ZSCORE, OP_VOCAB, OP_BUCKETIZE, OP_FILL_I64, OP_FILL_F32, OP_FILL_STR, OP_RATIO_LABEL) = range(7)
+
+
+class NativeError(RuntimeError):
+    """A libtaxi_xf entry point returned a non-zero status."""
+
+
+class TxfOp(Structure):
+    """struct txf_op (include/taxi_xf.h)."""
+
+    _fields_ = [
+        ("kind", c_int32), ("in_dtype", c_int32),
+        ("in0", c_void_p), ("valid0", c_void_p), ("in1", c_void_p), ("valid1", c_void_p),
+        ("pool", c_void_p), ("out", c_void_p), ("p0", c_void_p), ("p1", c_void_p),
+        ("a0", c_int64), ("a1", c_int64), ("a2", c_int64), ("a3", c_int64),
+        ("f0", c_float), ("reserved", c_int32),
+    ]
+
+
+if not os.path.exists(LIB_PATH):
+    raise ImportError(
+        f"{LIB_PATH} is missing: build it with `python __graft_entry__.py` (or "
+        "`python kubeflow-tfx-workshop_b200/build.py`). This package has no CPU fallback.")
+
+_lib = ctypes.CDLL(LIB_PATH)
+
+_PP = POINTER(c_void_p)
+_SIGNATURES = {
+    "txf_last_error": (c_char_p, []),
+    "txf_abi_version": (c_int, []),
+    "txf_launch_count": (c_int64, []),
+    "txf_moments_workspace_bytes": (c_size_t, [c_int]),
+    "txf_moments_update": (c_int, [_PP, _PP, POINTER(c_int32), c_int, c_int64, c_void_p, c_void_p, c_void_p]),
+    "txf_moments_merge": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p]),
+    "txf_moments_finalize": (c_int, [c_void_p, c_int, c_void_p, c_void_p]),
+    "txf_msel_state_bytes": (c_size_t, [c_int, c_int]),
+    "txf_msel_hist_bytes": (c_size_t, [c_int, c_int]),
+    "txf_msel_begin": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p]),
+    "txf_msel_hist": (c_int, [c_void_p, c_int, c_int, c_int, _PP, _PP, POINTER(c_int32), c_int, c_int64, c_void_p, c_void_p]),
+    "txf_msel_resolve": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p]),
+    "txf_msel_result": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p]),
+    "txf_qsample": (c_int, [_PP, _PP, POINTER(c_int32), c_int, c_int64, c_int64, c_uint64, c_void_p, c_void_p]),
+    "txf_qcount": (c_int, [_PP, _PP, POINTER(c_int32), c_int, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p]),
+    "txf_qresolve": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "txf_qfinal": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "txf_vocab_table_bytes": (c_size_t, [c_int64]),
+    "txf_vocab_lookup_bytes": (c_size_t, [c_int64]),
+    "txf_vocab_sort_scratch_bytes": (c_size_t, [c_int64]),
+    "txf_vocab_count": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p]),
+    "txf_vocab_compact": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "txf_vocab_export_meta": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "txf_vocab_export_bytes": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p]),
+    "txf_vocab_insert": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p]),
+    "txf_vocab_filter_ge": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "txf_vocab_sort": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
+    "txf_vocab_build_lookup": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p]),
+    "txf_vocab_lookup_from_terms": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p]),
+    "txf_transform": (c_int, [POINTER(TxfOp), c_int, c_int64, c_void_p]),
+    "txf_transform_launch_info": (c_int, [POINTER(c_int), POINTER(c_int), POINTER(c_int)]),
+    "txf_fingerprint64_batch": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
+}
+
+EXPORTED = sorted(_SIGNATURES)
+
+for _name, (_res, _args) in _SIGNATURES.items():
+    _fn = getattr(_lib, _name)  # AttributeError here == the library does not match the header
+    _fn.restype = _res
+    _fn.argtypes = _args
+
+
+def last_error() -> str:
+    return (_lib.txf_last_error() or b"").decode("utf-8", "replace")
+
+
+def call(name: str, *args):
+    """Call a status-returning entry point; raise NativeError with the library's message."""
+    rc = getattr(_lib, name)(*args)
+    if rc != 0:
+        raise NativeError(f"{name} failed ({rc}): {last_error()}")
+
+
+def query(name: str, *args):
+    """Call a size/version query (no status code)."""
+    return getattr(_lib, name)(*args)
+
+
+def ptr_array(ptrs):
+    """Host array of device pointers (None -> NULL)."""
+    arr = (c_void_p * len(ptrs))()
+    for i, p in enumerate(ptrs):
+        arr[i] = p if p else None
+    return arr
+
+
+def i32_array(vals):
+    return (c_int32 * len(vals))(*vals)
+
+
+def launch_count() -> int:
+    return int(_lib.txf_launch_count())

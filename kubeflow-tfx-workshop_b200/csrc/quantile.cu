@@ -1,0 +1,532 @@
+// quantile.cu -- quantile-boundary analyzer of tft.bucketize (reference call site
+// airflow-dags/taxi_utils.py:128-130; fill rule :86-103).
+//
+// Two engines, both EXACT (they return true order statistics, so the result is independent of
+// chunking, grid size and the number of GPUs; per-shard state merges by integer addition):
+//
+//  (1) txf_msel_*: multi-rank radix select, 4 passes x 8 bits over an order-preserving uint32
+//      key.  Works for any number of ranks; every element costs a shared-memory (or, for many
+//      ranks, global) atomic per pass.  Used on small inputs (the sample, the candidates, the
+//      vocabulary counts) and as the general fallback.
+//  (2) txf_qsample / txf_qcount / txf_qresolve / txf_qfinal: sample-select.  A stratified
+//      sample fixes a narrow bracket [lo_i, hi_i] around every target rank; ONE streaming pass
+//      over the column counts, per thread and without atomics, how many keys fall in each cell
+//      of the bracket grid and appends the few keys strictly inside a bracket to a candidate
+//      list; the exact answer is then an edge or a small selection among the candidates.
+//      Algorithmic bytes of that pass: 4 per row per f32 column + 1 validity bit.
+#include "common.cuh"
+
+namespace txf {
+
+// --------------------------------------------------------------------------------------------
+// element access shared by both engines
+// --------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t cell_key_f32(float v, bool present) { return f32_key(present ? v : 0.f); }
+__device__ __forceinline__ uint32_t cell_key_i64(long long v, bool present) {
+  return f32_key(present ? i64_to_f32(v) : 0.f);
+}
+
+// Calls f(key) for every row of column (values, valid, dtype) assigned to this thread;
+// quads are interleaved across the whole grid.x so loads coalesce into full lines.
+template <typename F>
+__device__ __forceinline__ void for_each_key(const void* values, const uint8_t* valid, int dtype, int64_t n, F f) {
+  const int64_t nquads = n >> 2;
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  int64_t q = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+  if (dtype == TXF_F32) {
+    const float* __restrict__ v = static_cast<const float*>(values);
+    for (; q + stride < nquads; q += 2 * stride) {
+      float4 a = ldg_f4(v + 4 * q), b = ldg_f4(v + 4 * (q + stride));
+      uint32_t ma = quad_valid(valid, 4 * q), mb = quad_valid(valid, 4 * (q + stride));
+      f(cell_key_f32(a.x, ma & 1)); f(cell_key_f32(a.y, ma & 2)); f(cell_key_f32(a.z, ma & 4)); f(cell_key_f32(a.w, ma & 8));
+      f(cell_key_f32(b.x, mb & 1)); f(cell_key_f32(b.y, mb & 2)); f(cell_key_f32(b.z, mb & 4)); f(cell_key_f32(b.w, mb & 8));
+    }
+    for (; q < nquads; q += stride) {
+      float4 a = ldg_f4(v + 4 * q);
+      uint32_t ma = quad_valid(valid, 4 * q);
+      f(cell_key_f32(a.x, ma & 1)); f(cell_key_f32(a.y, ma & 2)); f(cell_key_f32(a.z, ma & 4)); f(cell_key_f32(a.w, ma & 8));
+    }
+    if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+      int64_t i = (nquads << 2) + threadIdx.x;
+      f(cell_key_f32(v[i], row_valid(valid, i)));
+    }
+  } else {
+    const long long* __restrict__ v = static_cast<const long long*>(values);
+    for (; q < nquads; q += stride) {
+      longlong2 a = ldg_l2(v + 4 * q), b = ldg_l2(v + 4 * q + 2);
+      uint32_t ma = quad_valid(valid, 4 * q);
+      f(cell_key_i64(a.x, ma & 1)); f(cell_key_i64(a.y, ma & 2)); f(cell_key_i64(b.x, ma & 4)); f(cell_key_i64(b.y, ma & 8));
+    }
+    if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+      int64_t i = (nquads << 2) + threadIdx.x;
+      f(cell_key_i64(v[i], row_valid(valid, i)));
+    }
+  }
+}
+
+template <typename F>
+__device__ __forceinline__ void for_each_raw_key(const uint32_t* __restrict__ keys, int64_t n, F f) {
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < n; i += stride) f(keys[i]);
+}
+
+// --------------------------------------------------------------------------------------------
+// (1) multi-rank radix select
+// --------------------------------------------------------------------------------------------
+struct MselLayout {
+  size_t hist, rem, prefix, uprefix, slot, ucount, total;
+};
+__host__ __device__ inline MselLayout msel_layout(int ncols, int R) {
+  MselLayout L;
+  size_t cr = static_cast<size_t>(ncols) * R;
+  L.hist = 0;
+  L.rem = L.hist + cr * 256 * sizeof(uint64_t);
+  L.prefix = L.rem + cr * sizeof(uint64_t);
+  L.uprefix = L.prefix + cr * sizeof(uint32_t);
+  L.slot = L.uprefix + cr * sizeof(uint32_t);
+  L.ucount = L.slot + cr * sizeof(int32_t);
+  L.total = L.ucount + static_cast<size_t>(ncols) * sizeof(int32_t);
+  L.total = (L.total + 255) & ~static_cast<size_t>(255);
+  return L;
+}
+
+constexpr int kMselBlock = 256;
+constexpr int kMselSmemSlots = 32;  // privatised histogram for up to 32 distinct prefixes (32 KB)
+
+__global__ void msel_begin_kernel(uint8_t* state, int ncols, int R, const uint64_t* __restrict__ ranks) {
+  MselLayout L = msel_layout(ncols, R);
+  int c = blockIdx.x;
+  uint64_t* rem = reinterpret_cast<uint64_t*>(state + L.rem) + static_cast<size_t>(c) * R;
+  uint32_t* prefix = reinterpret_cast<uint32_t*>(state + L.prefix) + static_cast<size_t>(c) * R;
+  uint32_t* uprefix = reinterpret_cast<uint32_t*>(state + L.uprefix) + static_cast<size_t>(c) * R;
+  int32_t* slot = reinterpret_cast<int32_t*>(state + L.slot) + static_cast<size_t>(c) * R;
+  int32_t* ucount = reinterpret_cast<int32_t*>(state + L.ucount);
+  __shared__ int any;
+  if (threadIdx.x == 0) any = 0;
+  __syncthreads();
+  for (int i = threadIdx.x; i < R; i += blockDim.x) {
+    uint64_t r = ranks[static_cast<size_t>(c) * R + i];
+    rem[i] = r;
+    prefix[i] = 0;
+    uprefix[i] = 0;
+    slot[i] = r ? 0 : -1;
+    if (r) any = 1;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) ucount[c] = any;
+}
+
+template <int KIND>
+__global__ void __launch_bounds__(kMselBlock) msel_hist_kernel(uint8_t* state, int ncols, int R, int pass,
+                                                               NumColsView cols, int64_t n,
+                                                               const uint64_t* __restrict__ n_dev) {
+  extern __shared__ uint32_t smem[];
+  MselLayout L = msel_layout(ncols, R);
+  const int c = blockIdx.y;
+  const int U = reinterpret_cast<const int32_t*>(state + L.ucount)[c];
+  if (U == 0) return;
+  const uint32_t* g_upref = reinterpret_cast<const uint32_t*>(state + L.uprefix) + static_cast<size_t>(c) * R;
+  unsigned long long* hist = reinterpret_cast<unsigned long long*>(state + L.hist) + static_cast<size_t>(c) * R * 256;
+  uint32_t* s_upref = smem;                    // [R]
+  uint32_t* s_hist = smem + R;                 // [min(U,32)][256]
+  const bool priv = U <= kMselSmemSlots;
+  for (int i = threadIdx.x; i < U; i += kMselBlock) s_upref[i] = g_upref[i];
+  if (priv)
+    for (int i = threadIdx.x; i < U * 256; i += kMselBlock) s_hist[i] = 0;
+  __syncthreads();
+  const int pshift = 32 - 8 * pass;  // prefix = key >> pshift (pass 0: everything shares prefix 0)
+  const int dshift = 24 - 8 * pass;
+  if (KIND == 1 && n_dev != nullptr) {
+    int64_t nd = static_cast<int64_t>(n_dev[c]);
+    n = nd < n ? nd : n;
+  }
+  auto visit = [&](uint32_t key) {
+    uint32_t pre = pass == 0 ? 0u : (key >> pshift);
+    int lo = 0, len = U;  // lower_bound over the sorted distinct prefixes
+    while (len > 0) {
+      int half = len >> 1;
+      bool lt = s_upref[lo + half] < pre;
+      lo = lt ? lo + half + 1 : lo;
+      len = lt ? len - half - 1 : half;
+    }
+    if (lo < U && s_upref[lo] == pre) {
+      uint32_t bin = (static_cast<uint32_t>(lo) << 8) | ((key >> dshift) & 255u);
+      if (priv) {
+        atomicAdd(&s_hist[bin], 1u);
+      } else {  // many live prefixes: aggregate equal bins inside the warp, one global atomic each
+        unsigned peers = __match_any_sync(__activemask(), bin);
+        if (static_cast<int>(lane_id()) == __ffs(peers) - 1) atomicAdd(&hist[bin], static_cast<unsigned long long>(__popc(peers)));
+      }
+    }
+  };
+  if (KIND == 0)
+    for_each_key(cols.values[c], cols.valid[c], cols.dtype[c], n, visit);
+  else
+    for_each_raw_key(static_cast<const uint32_t*>(cols.values[c]), n, visit);
+  if (priv) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < U * 256; i += kMselBlock) {
+      uint32_t v = s_hist[i];
+      if (v) atomicAdd(&hist[i], static_cast<unsigned long long>(v));
+    }
+  }
+}
+
+__global__ void msel_resolve_kernel(uint8_t* state, int ncols, int R, int pass) {
+  MselLayout L = msel_layout(ncols, R);
+  const int c = blockIdx.x;
+  unsigned long long* hist = reinterpret_cast<unsigned long long*>(state + L.hist) + static_cast<size_t>(c) * R * 256;
+  uint64_t* rem = reinterpret_cast<uint64_t*>(state + L.rem) + static_cast<size_t>(c) * R;
+  uint32_t* prefix = reinterpret_cast<uint32_t*>(state + L.prefix) + static_cast<size_t>(c) * R;
+  uint32_t* uprefix = reinterpret_cast<uint32_t*>(state + L.uprefix) + static_cast<size_t>(c) * R;
+  int32_t* slot = reinterpret_cast<int32_t*>(state + L.slot) + static_cast<size_t>(c) * R;
+  int32_t* ucount = reinterpret_cast<int32_t*>(state + L.ucount);
+  const int U = ucount[c];
+  for (int i = threadIdx.x; i < R; i += blockDim.x) {
+    int s = slot[i];
+    if (s < 0) continue;
+    const unsigned long long* h = hist + static_cast<size_t>(s) * 256;
+    uint64_t r = rem[i], cum = 0;
+    int d = 255;
+    for (int b = 0; b < 256; ++b) {
+      uint64_t hb = h[b];
+      if (r <= cum + hb) { d = b; break; }
+      cum += hb;
+    }
+    if (d == 255 && r > cum + h[255]) cum = 0;  // rank beyond the data: keep going, result is meaningless
+    prefix[i] = (prefix[i] << 8) | static_cast<uint32_t>(d);
+    rem[i] = r - cum;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {  // rebuild the distinct-prefix table; ranks ascend, so prefixes ascend
+    int u = 0;
+    bool first = true;
+    uint32_t last = 0;
+    for (int i = 0; i < R; ++i) {
+      if (slot[i] < 0) continue;
+      uint32_t p = prefix[i];
+      if (first || p != last) { uprefix[u++] = p; last = p; first = false; }
+      slot[i] = u - 1;
+    }
+    ucount[c] = u;
+  }
+  for (int i = threadIdx.x; i < U * 256; i += blockDim.x) hist[i] = 0;  // ready for the next pass
+  (void)pass;
+}
+
+__global__ void msel_result_kernel(const uint8_t* state, int ncols, int R, uint32_t* __restrict__ out) {
+  MselLayout L = msel_layout(ncols, R);
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= ncols * R) return;
+  const uint32_t* prefix = reinterpret_cast<const uint32_t*>(state + L.prefix);
+  const int32_t* slot = reinterpret_cast<const int32_t*>(state + L.slot);
+  out[i] = slot[i] >= 0 ? prefix[i] : 0u;
+}
+
+// --------------------------------------------------------------------------------------------
+// (2) sample-select
+// --------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t mix64(uint64_t z) {
+  z += 0x9e3779b97f4a7c15ULL;
+  z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ULL;
+  z = (z ^ (z >> 27)) * 0x94d049bb133111ebULL;
+  return z ^ (z >> 31);
+}
+
+__global__ void qsample_kernel(NumColsView cols, int64_t n, int64_t M, uint64_t seed, uint32_t* __restrict__ out) {
+  const int c = blockIdx.y;
+  int64_t j = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+  if (j >= M) return;
+  const int64_t stride = n / M;  // >= 1 (caller guarantees M <= n)
+  int64_t row = j * stride + static_cast<int64_t>(mix64(seed ^ (static_cast<uint64_t>(j) * 0x2545F4914F6CDD1DULL)) %
+                                                  static_cast<uint64_t>(stride));
+  bool present = row_valid(cols.valid[c], row);
+  uint32_t key = cols.dtype[c] == TXF_F32
+                     ? cell_key_f32(static_cast<const float*>(cols.values[c])[row], present)
+                     : cell_key_i64(static_cast<const long long*>(cols.values[c])[row], present);
+  out[static_cast<size_t>(c) * M + j] = key;
+}
+
+constexpr int kQBlock = 256;
+
+// cells: 2p = strictly between edge p-1 and edge p (p = 0..E), 2p+1 = equal to edge p (p < E)
+__global__ void __launch_bounds__(kQBlock) qcount_kernel(NumColsView cols, int64_t n, int T,
+                                                         const uint32_t* __restrict__ edges_all,
+                                                         unsigned long long* __restrict__ cells_all,
+                                                         uint32_t* __restrict__ cand_all,
+                                                         unsigned long long* __restrict__ cand_count, int64_t cand_cap) {
+  extern __shared__ uint32_t smem[];
+  const int c = blockIdx.y;
+  const int E = 2 * T, ncell = 2 * E + 1;
+  uint32_t* s_edges = smem;                                            // [E]
+  uint16_t* s_cnt = reinterpret_cast<uint16_t*>(smem + ((E + 1) & ~1)); // [ncell][kQBlock], private per thread
+  for (int i = threadIdx.x; i < E; i += kQBlock) s_edges[i] = edges_all[static_cast<size_t>(c) * E + i];
+  for (int i = threadIdx.x; i < ncell * kQBlock; i += kQBlock) s_cnt[i] = 0;
+  __syncthreads();
+  uint32_t* cand = cand_all + static_cast<size_t>(c) * cand_cap;
+  // private 16-bit counter of (cell, thread): lanes of a warp sit in 32 different banks, warps w
+  // and w+4 share the words (low/high half), so the read-modify-write never bank-conflicts
+  const int my_slot = (((threadIdx.x >> 5) & 3) * 32 + static_cast<int>(lane_id())) * 2 + (threadIdx.x >> 7);
+  auto visit = [&](uint32_t key) {
+    int lo = 0, len = E;  // lo = number of edges < key
+    while (len > 0) {
+      int half = len >> 1;
+      bool lt = s_edges[lo + half] < key;
+      lo = lt ? lo + half + 1 : lo;
+      len = lt ? len - half - 1 : half;
+    }
+    bool eq = lo < E && s_edges[lo] == key;
+    int cell = 2 * lo + (eq ? 1 : 0);
+    s_cnt[cell * kQBlock + my_slot] += 1;      // <= 65535 keys per thread per launch (grid sizing)
+    if ((lo & 1) && !eq) {                     // strictly inside bracket (lo-1)/2: keep the key
+      unsigned peers = __activemask();
+      int leader = __ffs(peers) - 1;
+      unsigned long long base = 0;
+      if (static_cast<int>(lane_id()) == leader) base = atomicAdd(&cand_count[c], static_cast<unsigned long long>(__popc(peers)));
+      base = __shfl_sync(peers, base, leader);
+      unsigned long long pos = base + __popc(peers & ((1u << lane_id()) - 1u));
+      if (pos < static_cast<unsigned long long>(cand_cap)) cand[pos] = key;
+    }
+  };
+  for_each_key(cols.values[c], cols.valid[c], cols.dtype[c], n, visit);
+  __syncthreads();
+  // fold the private counters: warp w takes cells w, w+8, ...; lanes stride over the 256 threads
+  const int warp = threadIdx.x >> 5;
+  for (int cell = warp; cell < ncell; cell += kQBlock / 32) {
+    uint32_t s = 0;
+#pragma unroll
+    for (int j = 0; j < kQBlock / 32; ++j) s += s_cnt[cell * kQBlock + j * 32 + lane_id()];
+#pragma unroll
+    for (int off = 16; off; off >>= 1) s += __shfl_down_sync(0xffffffffu, s, off);
+    if (lane_id() == 0 && s) atomicAdd(&cells_all[static_cast<size_t>(c) * ncell + cell], static_cast<unsigned long long>(s));
+  }
+}
+
+__global__ void qresolve_kernel(const unsigned long long* __restrict__ cells_all, const uint32_t* __restrict__ edges_all,
+                                const unsigned long long* __restrict__ cand_count, int64_t cand_cap,
+                                const uint64_t* __restrict__ ranks, int ncols, int T, uint32_t* __restrict__ direct_key,
+                                uint64_t* __restrict__ cand_rank, int32_t* __restrict__ status) {
+  const int c = blockIdx.x;
+  const int E = 2 * T, ncell = 2 * E + 1;
+  const unsigned long long* cells = cells_all + static_cast<size_t>(c) * ncell;
+  const uint32_t* edges = edges_all + static_cast<size_t>(c) * E;
+  __shared__ int bad;
+  if (threadIdx.x == 0) bad = (cand_count[c] > static_cast<unsigned long long>(cand_cap)) ? 2 : 0;
+  __syncthreads();
+  for (int i = threadIdx.x; i < T; i += blockDim.x) {
+    const int jl = 2 * i, jh = 2 * i + 1;
+    const uint32_t el = edges[jl], eh = edges[jh];
+    // number of keys < edge j and == edge j, with duplicate edges collapsing onto the first copy
+    auto first_of = [&](int j) { while (j > 0 && edges[j - 1] == edges[j]) --j; return j; };
+    auto count_lt = [&](int j) {
+      int f = first_of(j);
+      unsigned long long s = cells[2 * f];
+      for (int p = 0; p < f; ++p) s += cells[2 * p] + cells[2 * p + 1];
+      return s;
+    };
+    auto count_eq = [&](int j) { return cells[2 * first_of(j) + 1]; };
+    const unsigned long long r = ranks[i];
+    const unsigned long long Ll = count_lt(jl), El = count_eq(jl);
+    uint32_t dk = 0;
+    uint64_t cr = 0;
+    int miss = 0;
+    if (r <= Ll) {
+      miss = 1;
+    } else if (r <= Ll + El) {
+      dk = el;
+    } else if (eh == el) {
+      miss = 1;
+    } else {
+      const unsigned long long Lh = count_lt(jh), Eh = count_eq(jh);
+      if (r <= Lh) {
+        unsigned long long before = 0;  // candidates of earlier brackets precede ours in key order
+        for (int k = 0; k < i; ++k) before += cells[2 * (2 * k + 1)];
+        cr = before + (r - Ll - El);
+      } else if (r <= Lh + Eh) {
+        dk = eh;
+      } else {
+        miss = 1;
+      }
+    }
+    direct_key[static_cast<size_t>(c) * T + i] = dk;
+    cand_rank[static_cast<size_t>(c) * T + i] = cr;
+    if (miss) bad = 1;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) status[c] = bad;
+}
+
+__global__ void qfinal_kernel(const uint32_t* __restrict__ direct_key, const uint64_t* __restrict__ cand_rank,
+                              const uint32_t* __restrict__ selected, int ncols, int T, float* __restrict__ boundaries,
+                              int32_t* __restrict__ nbound) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= ncols) return;
+  int m = 0;
+  uint32_t last = 0;
+  for (int i = 0; i < T; ++i) {
+    size_t k = static_cast<size_t>(c) * T + i;
+    uint32_t key = cand_rank[k] ? selected[k] : direct_key[k];
+    if (m == 0 || key != last) {  // tft returns DISTINCT boundaries (Appendix A.4 rule 3)
+      boundaries[static_cast<size_t>(c) * T + m++] = key_f32(key);
+      last = key;
+    }
+  }
+  nbound[c] = m;
+}
+
+static int fill_view(NumColsView& v, const void* const* values, const uint8_t* const* valid, const int32_t* dtype,
+                     int ncols, const char* who, bool raw) {
+  TXF_REQUIRE(ncols >= 1 && ncols <= TXF_MAX_COLS, "%s: ncols=%d out of [1,%d]", who, ncols, TXF_MAX_COLS);
+  TXF_REQUIRE(values != nullptr, "%s: null column table", who);
+  for (int c = 0; c < ncols; ++c) {
+    TXF_REQUIRE(values[c] != nullptr && aligned(values[c], 16), "%s: column %d values null or not 16B aligned", who, c);
+    v.values[c] = values[c];
+    v.valid[c] = (valid && !raw) ? valid[c] : nullptr;
+    v.dtype[c] = (dtype && !raw) ? dtype[c] : TXF_F32;
+    TXF_REQUIRE(v.dtype[c] == TXF_F32 || v.dtype[c] == TXF_I64, "%s: column %d bad dtype", who, c);
+  }
+  return TXF_OK;
+}
+
+// grid.x for a (grid.x, ncols) streaming launch: one resident wave, at least 128 CTAs per column
+static int stream_grid(int64_t n, int block, int ctas_per_sm, int ncols) {
+  int64_t want = ((n >> 2) + block) / block;
+  int64_t cap = static_cast<int64_t>(kSMs) * ctas_per_sm / ncols;
+  if (cap < 128) cap = 128;
+  return static_cast<int>(want < cap ? (want < 1 ? 1 : want) : cap);
+}
+
+}  // namespace txf
+
+extern "C" {
+
+size_t txf_msel_state_bytes(int ncols, int R) { return txf::msel_layout(ncols, R).total; }
+size_t txf_msel_hist_bytes(int ncols, int R) { return txf::msel_layout(ncols, R).rem; }
+
+int txf_msel_begin(void* state_dev, int ncols, int R, const uint64_t* ranks_dev, txf_stream_t stream) {
+  using namespace txf;
+  TXF_REQUIRE(ncols >= 1 && ncols <= TXF_MAX_COLS && R >= 1 && R <= 4096, "msel_begin: bad sizes ncols=%d R=%d", ncols, R);
+  TXF_REQUIRE(state_dev && ranks_dev, "msel_begin: null pointer");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  TXF_CUDA(cudaMemsetAsync(state_dev, 0, msel_layout(ncols, R).rem, s));
+  msel_begin_kernel<<<ncols, 128, 0, s>>>(static_cast<uint8_t*>(state_dev), ncols, R, ranks_dev);
+  TXF_LAUNCH_CHECK();
+  count_launch(1);
+  return TXF_OK;
+}
+
+int txf_msel_hist(void* state_dev, int ncols, int R, int pass, const void* const* data, const uint8_t* const* valid,
+                  const int32_t* dtype, int kind, int64_t n, const uint64_t* n_dev, txf_stream_t stream) {
+  using namespace txf;
+  TXF_REQUIRE(state_dev != nullptr, "msel_hist: null state");
+  TXF_REQUIRE(R >= 1 && R <= 4096 && pass >= 0 && pass < 4, "msel_hist: bad R/pass");
+  TXF_REQUIRE(kind == 0 || kind == 1, "msel_hist: kind must be 0 (cells) or 1 (raw keys)");
+  TXF_REQUIRE(n >= 0 && n < (1LL << 31), "msel_hist: n out of range");
+  if (n == 0) return TXF_OK;
+  NumColsView v{};
+  int rc = fill_view(v, data, valid, dtype, ncols, "msel_hist", kind == 1);
+  if (rc) return rc;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  size_t smem = (static_cast<size_t>(R) + static_cast<size_t>(R < kMselSmemSlots ? R : kMselSmemSlots) * 256) * sizeof(uint32_t);
+  dim3 grid(stream_grid(kind == 0 ? n : n * 4, kMselBlock, 4, ncols), ncols);
+  if (kind == 0)
+    msel_hist_kernel<0><<<grid, kMselBlock, smem, s>>>(static_cast<uint8_t*>(state_dev), ncols, R, pass, v, n, n_dev);
+  else
+    msel_hist_kernel<1><<<grid, kMselBlock, smem, s>>>(static_cast<uint8_t*>(state_dev), ncols, R, pass, v, n, n_dev);
+  TXF_LAUNCH_CHECK();
+  count_launch(1);
+  return TXF_OK;
+}
+
+int txf_msel_resolve(void* state_dev, int ncols, int R, int pass, txf_stream_t stream) {
+  using namespace txf;
+  TXF_REQUIRE(state_dev != nullptr && ncols >= 1 && ncols <= TXF_MAX_COLS && R >= 1 && R <= 4096, "msel_resolve: bad args");
+  msel_resolve_kernel<<<ncols, 256, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<uint8_t*>(state_dev), ncols, R, pass);
+  TXF_LAUNCH_CHECK();
+  count_launch(1);
+  return TXF_OK;
+}
+
+int txf_msel_result(const void* state_dev, int ncols, int R, uint32_t* keys_out_dev, txf_stream_t stream) {
+  using namespace txf;
+  TXF_REQUIRE(state_dev && keys_out_dev && ncols >= 1 && ncols <= TXF_MAX_COLS && R >= 1 && R <= 4096, "msel_result: bad args");
+  int total = ncols * R;
+  msel_result_kernel<<<(total + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const uint8_t*>(state_dev), ncols, R, keys_out_dev);
+  TXF_LAUNCH_CHECK();
+  count_launch(1);
+  return TXF_OK;
+}
+
+int txf_qsample(const void* const* values, const uint8_t* const* valid, const int32_t* dtype, int ncols, int64_t n,
+                int64_t M, uint64_t seed, uint32_t* sample_dev, txf_stream_t stream) {
+  using namespace txf;
+  TXF_REQUIRE(n >= 1 && n < (1LL << 31) && M >= 1 && M <= n, "qsample: need 1 <= M <= n < 2^31");
+  TXF_REQUIRE(sample_dev != nullptr, "qsample: null output");
+  NumColsView v{};
+  int rc = fill_view(v, values, valid, dtype, ncols, "qsample", false);
+  if (rc) return rc;
+  dim3 grid(static_cast<unsigned>((M + 255) / 256), ncols);
+  qsample_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(v, n, M, seed, sample_dev);
+  TXF_LAUNCH_CHECK();
+  count_launch(1);
+  return TXF_OK;
+}
+
+int txf_qcount(const void* const* values, const uint8_t* const* valid, const int32_t* dtype, int ncols, int64_t n, int T,
+               const uint32_t* edges_dev, uint64_t* cells_dev, uint32_t* cand_dev, uint64_t* cand_count_dev,
+               int64_t cand_cap, txf_stream_t stream) {
+  using namespace txf;
+  TXF_REQUIRE(T >= 1 && T <= TXF_QMAX_TARGETS, "qcount: T=%d out of [1,%d]", T, TXF_QMAX_TARGETS);
+  TXF_REQUIRE(n >= 0 && n < (1LL << 31), "qcount: n out of range");
+  TXF_REQUIRE(edges_dev && cells_dev && cand_dev && cand_count_dev && cand_cap >= 1, "qcount: null pointer / empty candidate buffer");
+  if (n == 0) return TXF_OK;
+  NumColsView v{};
+  int rc = fill_view(v, values, valid, dtype, ncols, "qcount", false);
+  if (rc) return rc;
+  const int E = 2 * T, ncell = 2 * E + 1;
+  size_t smem = static_cast<size_t>((E + 1) & ~1) * 4 + static_cast<size_t>(ncell) * kQBlock * 2;
+  if (smem > 48 * 1024)
+    TXF_CUDA(cudaFuncSetAttribute(qcount_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+  int per_sm = static_cast<int>((200 * 1024) / (smem + 1024));
+  per_sm = per_sm < 1 ? 1 : (per_sm > 6 ? 6 : per_sm);
+  dim3 grid(stream_grid(n, kQBlock, per_sm, ncols), ncols);
+  // private 16-bit counters: every thread must see fewer than 65536 keys
+  TXF_REQUIRE(n / (static_cast<int64_t>(grid.x) * kQBlock) + 8 < 65536, "qcount: chunk too large for 16-bit counters");
+  qcount_kernel<<<grid, kQBlock, smem, static_cast<cudaStream_t>(stream)>>>(
+      v, n, T, edges_dev, reinterpret_cast<unsigned long long*>(cells_dev), cand_dev,
+      reinterpret_cast<unsigned long long*>(cand_count_dev), cand_cap);
+  TXF_LAUNCH_CHECK();
+  count_launch(1);
+  return TXF_OK;
+}
+
+int txf_qresolve(const uint64_t* cells_dev, const uint32_t* edges_dev, const uint64_t* cand_count_dev, int64_t cand_cap,
+                 const uint64_t* target_ranks_dev, int ncols, int T, uint32_t* direct_key_dev, uint64_t* cand_rank_dev,
+                 int32_t* status_dev, txf_stream_t stream) {
+  using namespace txf;
+  TXF_REQUIRE(ncols >= 1 && ncols <= TXF_MAX_COLS && T >= 1 && T <= TXF_QMAX_TARGETS, "qresolve: bad sizes");
+  TXF_REQUIRE(cells_dev && edges_dev && cand_count_dev && target_ranks_dev && direct_key_dev && cand_rank_dev && status_dev,
+              "qresolve: null pointer");
+  qresolve_kernel<<<ncols, 64, 0, static_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const unsigned long long*>(cells_dev), edges_dev,
+      reinterpret_cast<const unsigned long long*>(cand_count_dev), cand_cap, target_ranks_dev, ncols, T, direct_key_dev,
+      cand_rank_dev, status_dev);
+  TXF_LAUNCH_CHECK();
+  count_launch(1);
+  return TXF_OK;
+}
+
+int txf_qfinal(const uint32_t* direct_key_dev, const uint64_t* cand_rank_dev, const uint32_t* selected_key_dev, int ncols,
+               int T, float* boundaries_dev, int32_t* nbound_dev, txf_stream_t stream) {
+  using namespace txf;
+  TXF_REQUIRE(ncols >= 1 && ncols <= TXF_MAX_COLS && T >= 1 && T <= 4096, "qfinal: bad sizes");
+  TXF_REQUIRE(direct_key_dev && cand_rank_dev && selected_key_dev && boundaries_dev && nbound_dev, "qfinal: null pointer");
+  qfinal_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(direct_key_dev, cand_rank_dev, selected_key_dev, ncols, T,
+                                                               boundaries_dev, nbound_dev);
+  TXF_LAUNCH_CHECK();
+  count_launch(1);
+  return TXF_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,430 @@
+// transform.cu -- the fused per-row phase of preprocessing_fn (reference:
+// airflow-dags/taxi_utils.py:115-145).  ONE persistent kernel (one CTA per SM) runs the whole
+// program of column ops: fill-missing (:86-103), z-score (:116-119), vocabulary lookup with OOV
+// hashing (:121-126), bucketize (:128-130), categorical pass-through (:132-133) and the tips
+// label (:135-143).  The program is walked op-major: all SMs stream the same input column and
+// the same output column at any moment (two sequential DRAM streams instead of 35 interleaved
+// ones), and no grid-wide barrier separates the ops.
+//
+// Memory-bound by construction: every input cell is read once with 16-byte loads, every output
+// written once with 16-byte streaming stores; the small read-mostly state (bucket boundaries,
+// vocabulary lookup tables) is staged in shared memory once per CTA.
+// Algorithmic bytes per row (taxi schema): read 98.1 + Lp + Lc, write 120; the
+// label re-reads `fare` (4 B/row) because ops run column by column.
+#include "vocab.cuh"
+
+namespace txf {
+
+constexpr int kXfBlock = 1024;
+constexpr int kXfUnroll = 4;                                   // quads in flight per thread and op
+constexpr int64_t kXfTileRows = 4LL * kXfBlock * kXfUnroll;    // 16384 rows per tile
+constexpr int kXfSmemBudget = 200 * 1024;
+
+struct XfOp {                // device-side op (txf_op + staging offsets)
+  int32_t kind, in_dtype;
+  const void* in0;
+  const uint8_t* valid0;
+  const void* in1;
+  const uint8_t* valid1;
+  const uint8_t* pool;
+  void* out;
+  const void* p0;
+  const void* p1;
+  int64_t a0, a1, a2, a3;
+  float f0;
+  int32_t smem_off;          // byte offset of this op's staged state, -1 = read it from global
+};
+struct XfProgram {
+  XfOp ops[TXF_MAX_OPS];
+  int32_t nops;
+  int32_t smem_bytes;
+};
+
+// ---- element math (shared by the vector path and the scalar tail) ---------------------------
+// (x - mean) / den.  div.rn compiles to an inline fast path plus a CALL to a slow-path routine;
+// that call site made ptxas spill every live register of the streaming loop.  Since den is the
+// same for every row, its correctly rounded reciprocal is computed once per op, and the quotient
+// is one multiply plus a Markstein FMA correction: the IEEE-rounded quotient whenever nothing
+// over/underflows (non-finite quotients are returned as the plain product).
+struct ZScale {
+  float mean, den, rden;
+};
+__device__ __forceinline__ ZScale make_zscale(const float* mv) {
+  ZScale z;
+  z.mean = mv[0];
+  z.den = __fsqrt_rn(mv[1]);
+  z.rden = z.den != 0.f ? __frcp_rn(z.den) : 0.f;
+  return z;
+}
+__device__ __forceinline__ float zscore1(float x, const ZScale& z) {
+  float num = __fsub_rn(x, z.mean);
+  if (z.den == 0.f) return num;  // var == 0 -> x - mean (tft rule)
+  float q = __fmul_rn(num, z.rden);
+  float r = __fmaf_rn(-z.den, q, num);
+  float q2 = __fmaf_rn(r, z.rden, q);
+  return fabsf(q) < __int_as_float(0x7f800000) ? q2 : q;
+}
+__device__ __forceinline__ long long bucket1(float x, const float* __restrict__ b, int nb) {
+  int lo = 0, len = nb;  // upper_bound: count of leading boundaries with !(x < b); NaN -> nb
+  while (len > 0) {
+    int half = len >> 1;
+    bool go = !(x < b[lo + half]);
+    lo = go ? lo + half + 1 : lo;
+    len = go ? len - half - 1 : half;
+  }
+  return lo;
+}
+__device__ __forceinline__ long long label1(float fare, float tips, float ratio) {
+  float thr = __fmul_rn(fare, ratio);  // fp32 product, never contracted
+  return (fare != fare) ? 0LL : (tips > thr ? 1LL : 0LL);
+}
+// x % d without the 64-bit division subroutine (a CALL inside the row loop).  d <= 65535: three
+// 32-bit remainders; otherwise shift-subtract long division (only for huge num_oov_buckets).
+__device__ __forceinline__ uint64_t mod_u64(uint64_t x, uint64_t d) {
+  if (d <= 65535u) {
+    uint32_t dd = static_cast<uint32_t>(d);
+    uint32_t hi = static_cast<uint32_t>(x >> 32), lo = static_cast<uint32_t>(x);
+    uint32_t c = (0xFFFFFFFFu % dd + 1u) % dd;  // 2^32 mod d
+    return ((hi % dd) * c % dd + lo % dd) % dd;
+  }
+  uint64_t r = 0;
+#pragma unroll 1
+  for (int i = 63; i >= 0; --i) {
+    uint64_t top = r >> 63;
+    r = (r << 1) | ((x >> i) & 1ULL);
+    if (top || r >= d) r -= d;
+  }
+  return r;
+}
+__device__ __forceinline__ long long vocab1(const uint8_t* str, uint32_t len, const LookupSlot* __restrict__ lut,
+                                            uint64_t mask, long long vocab_size, long long num_oov, long long dflt) {
+  uint64_t fp, tag;
+  fingerprint128(str, len, fp, tag);
+  unsigned long long kfp, ktag;
+  table_identity(fp, tag, kfp, ktag);
+  const uint32_t tag32 = static_cast<uint32_t>(ktag);
+  uint64_t idx = home_slot(kfp, mask);
+  for (uint64_t probe = 0; probe <= mask; ++probe, idx = (idx + 1) & mask) {
+    const uint4 raw = *reinterpret_cast<const uint4*>(lut + idx);
+    const unsigned long long sfp = (static_cast<unsigned long long>(raw.y) << 32) | raw.x;
+    if (sfp == 0) break;
+    if (sfp == kfp && raw.z == tag32) return static_cast<int32_t>(raw.w);
+  }
+  if (num_oov <= 0) return dflt;
+  return vocab_size + static_cast<long long>(mod_u64(fp, static_cast<uint64_t>(num_oov)));
+}
+
+__device__ __forceinline__ float cell_f32(const XfOp& op, int64_t row) {  // fill + cast of one cell
+  bool v = row_valid(op.valid0, row);
+  if (op.in_dtype == TXF_F32) return v ? static_cast<const float*>(op.in0)[row] : 0.f;
+  return v ? i64_to_f32(static_cast<const long long*>(op.in0)[row]) : 0.f;
+}
+
+// one row of one op (tail rows only)
+__device__ void op_row(const XfOp& op, const uint8_t* smem, int64_t row, int64_t n) {
+  switch (op.kind) {
+    case TXF_OP_ZSCORE: {
+      static_cast<float*>(op.out)[row] = zscore1(cell_f32(op, row), make_zscale(static_cast<const float*>(op.p0)));
+      break;
+    }
+    case TXF_OP_BUCKETIZE: {
+      const float* b = op.smem_off >= 0 ? reinterpret_cast<const float*>(smem + op.smem_off) : static_cast<const float*>(op.p0);
+      int nb = *static_cast<const int32_t*>(op.p1);
+      static_cast<long long*>(op.out)[row] = bucket1(cell_f32(op, row), b, nb);
+      break;
+    }
+    case TXF_OP_FILL_I64:
+      static_cast<long long*>(op.out)[row] = row_valid(op.valid0, row) ? static_cast<const long long*>(op.in0)[row] : 0LL;
+      break;
+    case TXF_OP_FILL_F32:
+      static_cast<float*>(op.out)[row] = row_valid(op.valid0, row) ? static_cast<const float*>(op.in0)[row] : 0.f;
+      break;
+    case TXF_OP_FILL_STR: {
+      const int32_t* off = static_cast<const int32_t*>(op.in0);
+      int32_t base = off[0];
+      static_cast<int32_t*>(op.out)[row] = off[row] - base;
+      if (row == n - 1) static_cast<int32_t*>(op.out)[n] = off[n] - base;
+      break;
+    }
+    case TXF_OP_RATIO_LABEL: {
+      float fare = row_valid(op.valid0, row) ? static_cast<const float*>(op.in0)[row] : 0.f;
+      float tips = row_valid(op.valid1, row) ? static_cast<const float*>(op.in1)[row] : 0.f;
+      static_cast<long long*>(op.out)[row] = label1(fare, tips, op.f0);
+      break;
+    }
+    default: break;  // TXF_OP_VOCAB has no quad path: its row loop covers the tail
+  }
+}
+
+__device__ __forceinline__ void store_i64x4(long long* out, int64_t r, long long a, long long b, long long c, long long d) {
+  stcs_l2(out + r, make_longlong2(a, b));
+  stcs_l2(out + r + 2, make_longlong2(c, d));
+}
+
+// ---- op bodies.  Three loop nests only -- 4-byte inputs, 8-byte inputs, strings -- with the
+// op-specific arithmetic selected by a CTA-uniform switch INSIDE the loop.  (One loop nest per
+// op kind, inlined or called, made ptxas keep the loaded quads in local memory.)
+// A tile is kXfBlock * kXfUnroll quads; tiles are dealt round-robin to CTAs; thread t owns quads
+// q0 + t + j*kXfBlock of a tile.  4-byte inputs keep 4 quads (64 B) in flight per thread, 8-byte
+// inputs 2 quads (64 B).
+#define TXF_FOR_EACH_TILE(nquads_)                                                                  \
+  for (int64_t q0 = static_cast<int64_t>(blockIdx.x) * (kXfBlock * kXfUnroll) + threadIdx.x,        \
+               qstep = static_cast<int64_t>(gridDim.x) * (kXfBlock * kXfUnroll),                     \
+               qtile = static_cast<int64_t>(blockIdx.x) * (kXfBlock * kXfUnroll);                    \
+       qtile < (nquads_); q0 += qstep, qtile += qstep)
+
+__device__ __forceinline__ float4 fill_f4(float4 r, uint32_t m) {
+  return make_float4(m & 1 ? r.x : 0.f, m & 2 ? r.y : 0.f, m & 4 ? r.z : 0.f, m & 8 ? r.w : 0.f);
+}
+
+struct NumParams {  // per-op constants of the numeric kinds
+  ZScale z;
+  const float* b;
+  int nb;
+  float ratio;
+  int32_t base;
+};
+__device__ __forceinline__ NumParams make_params(const XfOp& op, const uint8_t* smem) {
+  NumParams p{};
+  if (op.kind == TXF_OP_ZSCORE) p.z = make_zscale(static_cast<const float*>(op.p0));
+  if (op.kind == TXF_OP_BUCKETIZE) {
+    p.b = op.smem_off >= 0 ? reinterpret_cast<const float*>(smem + op.smem_off) : static_cast<const float*>(op.p0);
+    p.nb = *static_cast<const int32_t*>(op.p1);
+  }
+  if (op.kind == TXF_OP_RATIO_LABEL) p.ratio = op.f0;
+  if (op.kind == TXF_OP_FILL_STR) p.base = __ldg(static_cast<const int32_t*>(op.in0));
+  return p;
+}
+
+// ops whose input cells are 4 bytes: fp32 z-score / bucketize / fill / label, string offsets
+__device__ __forceinline__ void run_in4(const XfOp& op, const uint8_t* smem, int64_t nquads) {
+  const NumParams p = make_params(op, smem);
+  const int kind = op.kind;
+  const float* __restrict__ v = static_cast<const float*>(op.in0);
+  const float* __restrict__ v1 = static_cast<const float*>(op.in1);
+  const uint8_t* __restrict__ valid = kind == TXF_OP_FILL_STR ? nullptr : op.valid0;
+  const uint8_t* __restrict__ valid1 = op.valid1;
+  void* out = op.out;
+  TXF_FOR_EACH_TILE(nquads) {
+    float4 raw[4];
+    uint32_t m[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      int64_t q = q0 + static_cast<int64_t>(u) * kXfBlock;
+      raw[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      m[u] = 0;
+      if (q < nquads) { raw[u] = ldg_f4(v + 4 * q); m[u] = quad_valid(valid, 4 * q); }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      int64_t q = q0 + static_cast<int64_t>(u) * kXfBlock;
+      if (q >= nquads) continue;
+      const float4 x = fill_f4(raw[u], m[u]);
+      switch (kind) {
+        case TXF_OP_ZSCORE:
+          stcs_f4(static_cast<float*>(out) + 4 * q, make_float4(zscore1(x.x, p.z), zscore1(x.y, p.z), zscore1(x.z, p.z), zscore1(x.w, p.z)));
+          break;
+        case TXF_OP_FILL_F32:
+          stcs_f4(static_cast<float*>(out) + 4 * q, x);
+          break;
+        case TXF_OP_FILL_STR: {
+          int4 o = make_int4(__float_as_int(raw[u].x) - p.base, __float_as_int(raw[u].y) - p.base, __float_as_int(raw[u].z) - p.base,
+                             __float_as_int(raw[u].w) - p.base);
+          stcs_i4(static_cast<int32_t*>(out) + 4 * q, o);
+          break;
+        }
+        case TXF_OP_BUCKETIZE:
+          store_i64x4(static_cast<long long*>(out), 4 * q, bucket1(x.x, p.b, p.nb), bucket1(x.y, p.b, p.nb), bucket1(x.z, p.b, p.nb),
+                      bucket1(x.w, p.b, p.nb));
+          break;
+        default: {  // TXF_OP_RATIO_LABEL: second fp32 column (tips)
+          const float4 t = fill_f4(ldg_f4(v1 + 4 * q), quad_valid(valid1, 4 * q));
+          store_i64x4(static_cast<long long*>(out), 4 * q, label1(x.x, t.x, p.ratio), label1(x.y, t.y, p.ratio), label1(x.z, t.z, p.ratio),
+                      label1(x.w, t.w, p.ratio));
+          break;
+        }
+      }
+    }
+  }
+  // offsets has n + 1 entries; entry n is written here when n % 4 == 0, else by the scalar tail
+  if (kind == TXF_OP_FILL_STR && blockIdx.x == 0 && threadIdx.x == 0) {
+    const int32_t* off = static_cast<const int32_t*>(op.in0);
+    static_cast<int32_t*>(out)[4 * nquads] = off[4 * nquads] - p.base;
+  }
+}
+
+// ops whose input cells are 8 bytes: int64 z-score / bucketize / fill
+__device__ __forceinline__ void run_in8(const XfOp& op, const uint8_t* smem, int64_t nquads) {
+  const NumParams p = make_params(op, smem);
+  const int kind = op.kind;
+  const long long* __restrict__ v = static_cast<const long long*>(op.in0);
+  const uint8_t* __restrict__ valid = op.valid0;
+  void* out = op.out;
+  TXF_FOR_EACH_TILE(nquads) {
+#pragma unroll 1
+    for (int h = 0; h < 2; ++h) {
+      longlong2 ra[2], rb[2];
+      uint32_t m[2];
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        int64_t q = q0 + static_cast<int64_t>(2 * h + u) * kXfBlock;
+        ra[u] = make_longlong2(0, 0); rb[u] = make_longlong2(0, 0); m[u] = 0;
+        if (q < nquads) { ra[u] = ldg_l2(v + 4 * q); rb[u] = ldg_l2(v + 4 * q + 2); m[u] = quad_valid(valid, 4 * q); }
+      }
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        int64_t q = q0 + static_cast<int64_t>(2 * h + u) * kXfBlock;
+        if (q >= nquads) continue;
+        const long long a = m[u] & 1 ? ra[u].x : 0LL, b = m[u] & 2 ? ra[u].y : 0LL, c = m[u] & 4 ? rb[u].x : 0LL,
+                        d = m[u] & 8 ? rb[u].y : 0LL;
+        switch (kind) {
+          case TXF_OP_FILL_I64:
+            store_i64x4(static_cast<long long*>(out), 4 * q, a, b, c, d);
+            break;
+          case TXF_OP_ZSCORE:
+            stcs_f4(static_cast<float*>(out) + 4 * q, make_float4(zscore1(i64_to_f32(a), p.z), zscore1(i64_to_f32(b), p.z),
+                                                                  zscore1(i64_to_f32(c), p.z), zscore1(i64_to_f32(d), p.z)));
+            break;
+          default:  // TXF_OP_BUCKETIZE
+            store_i64x4(static_cast<long long*>(out), 4 * q, bucket1(i64_to_f32(a), p.b, p.nb), bucket1(i64_to_f32(b), p.b, p.nb),
+                        bucket1(i64_to_f32(c), p.b, p.nb), bucket1(i64_to_f32(d), p.b, p.nb));
+            break;
+        }
+      }
+    }
+  }
+}
+
+// one row per lane: coalesced offsets, neighbouring term bytes, coalesced ids
+__device__ __forceinline__ void run_vocab(const XfOp& op, const uint8_t* smem, int64_t n) {
+  const int32_t* __restrict__ off = static_cast<const int32_t*>(op.in0);
+  const uint8_t* __restrict__ valid = op.valid0;
+  const uint8_t* __restrict__ pool = op.pool;
+  const LookupSlot* lut = op.smem_off >= 0 ? reinterpret_cast<const LookupSlot*>(smem + op.smem_off)
+                                            : static_cast<const LookupSlot*>(op.p0);
+  const uint64_t mask = static_cast<uint64_t>(op.a0 - 1);
+  const long long vocab_size = op.a1, num_oov = op.a2, dflt = op.a3;
+  long long* out = static_cast<long long*>(op.out);
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * kXfBlock;
+  for (int64_t row = static_cast<int64_t>(blockIdx.x) * kXfBlock + threadIdx.x; row < n; row += stride) {
+    int32_t b = __ldg(off + row), e = __ldg(off + row + 1);
+    bool v = row_valid(valid, row);
+    __stcs(out + row, vocab1(pool + b, v ? static_cast<uint32_t>(e - b) : 0u, lut, mask, vocab_size, num_oov, dflt));
+  }
+}
+
+__global__ void __launch_bounds__(kXfBlock, 1) transform_kernel(const __grid_constant__ XfProgram prog, int64_t n) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  // the op table is copied to shared memory so the tile functions can take plain pointers to it
+  __shared__ XfOp s_ops[TXF_MAX_OPS];
+  const int nops = prog.nops;
+  {
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(&prog.ops[0]);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(&s_ops[0]);
+    for (int i = threadIdx.x; i < nops * static_cast<int>(sizeof(XfOp) / 4); i += kXfBlock) dst[i] = src[i];
+  }
+  __syncthreads();
+  // ---- stage read-mostly state once per CTA ----------------------------------------------
+  for (int o = 0; o < nops; ++o) {
+    const XfOp& op = s_ops[o];
+    if (op.smem_off < 0) continue;
+    if (op.kind == TXF_OP_BUCKETIZE) {
+      int nb = *static_cast<const int32_t*>(op.p1);
+      float* dst = reinterpret_cast<float*>(smem + op.smem_off);
+      for (int i = threadIdx.x; i < nb; i += kXfBlock) dst[i] = static_cast<const float*>(op.p0)[i];
+    } else if (op.kind == TXF_OP_VOCAB) {
+      uint4* dst = reinterpret_cast<uint4*>(smem + op.smem_off);
+      const uint4* src = static_cast<const uint4*>(op.p0);
+      for (int64_t i = threadIdx.x; i < op.a0; i += kXfBlock) dst[i] = src[i];
+    }
+  }
+  __syncthreads();
+
+  const int64_t nquads = n >> 2;
+  for (int o = 0; o < nops; ++o) {
+    const XfOp& op = s_ops[o];
+    if (op.kind == TXF_OP_VOCAB)
+      run_vocab(op, smem, n);
+    else if (op.kind == TXF_OP_FILL_I64 || ((op.kind == TXF_OP_ZSCORE || op.kind == TXF_OP_BUCKETIZE) && op.in_dtype == TXF_I64))
+      run_in8(op, smem, nquads);
+    else
+      run_in4(op, smem, nquads);
+  }
+  // ---- rows past the last full quad (at most 3) -------------------------------------------
+  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+    int64_t row = (nquads << 2) + threadIdx.x;
+    for (int o = 0; o < nops; ++o) op_row(s_ops[o], smem, row, n);
+  }
+}
+
+static int g_last_grid = 0, g_last_block = 0, g_last_smem = 0;
+
+}  // namespace txf
+
+extern "C" {
+
+int txf_transform(const txf_op* ops, int nops, int64_t n, txf_stream_t stream) {
+  using namespace txf;
+  TXF_REQUIRE(ops != nullptr && nops >= 1 && nops <= TXF_MAX_OPS, "transform: nops=%d out of [1,%d]", nops, TXF_MAX_OPS);
+  TXF_REQUIRE(n >= 0 && n < (1LL << 31), "transform: n out of range");
+  if (n == 0) return TXF_OK;
+  XfProgram prog{};
+  prog.nops = nops;
+  int smem = 0;
+  for (int o = 0; o < nops; ++o) {
+    const txf_op& s = ops[o];
+    XfOp& d = prog.ops[o];
+    d.kind = s.kind; d.in_dtype = s.in_dtype; d.in0 = s.in0; d.valid0 = s.valid0; d.in1 = s.in1; d.valid1 = s.valid1;
+    d.pool = s.pool; d.out = s.out; d.p0 = s.p0; d.p1 = s.p1; d.a0 = s.a0; d.a1 = s.a1; d.a2 = s.a2; d.a3 = s.a3; d.f0 = s.f0;
+    d.smem_off = -1;
+    TXF_REQUIRE(s.in0 != nullptr && s.out != nullptr, "transform: op %d has a null input/output", o);
+    TXF_REQUIRE(aligned(s.in0, 16) && aligned(s.out, 16), "transform: op %d input/output not 16B aligned", o);
+    switch (s.kind) {
+      case TXF_OP_ZSCORE:
+        TXF_REQUIRE(s.p0 != nullptr, "transform: op %d (z-score) needs p0 = {mean,var}", o);
+        TXF_REQUIRE(s.in_dtype == TXF_F32 || s.in_dtype == TXF_I64, "transform: op %d bad dtype", o);
+        break;
+      case TXF_OP_BUCKETIZE: {
+        TXF_REQUIRE(s.p0 != nullptr && s.p1 != nullptr && s.a0 >= 0, "transform: op %d (bucketize) needs boundaries, count and capacity a0", o);
+        TXF_REQUIRE(s.in_dtype == TXF_F32 || s.in_dtype == TXF_I64, "transform: op %d bad dtype", o);
+        int need = static_cast<int>((s.a0 * 4 + 15) & ~15LL);
+        if (smem + need <= kXfSmemBudget) { d.smem_off = smem; smem += need; }
+        break;
+      }
+      case TXF_OP_VOCAB: {
+        TXF_REQUIRE(s.p0 != nullptr && s.pool != nullptr, "transform: op %d (vocabulary) needs lookup table and pool", o);
+        TXF_REQUIRE(s.a0 >= 2 && (s.a0 & (s.a0 - 1)) == 0, "transform: op %d lookup capacity must be a power of two", o);
+        TXF_REQUIRE(aligned(s.p0, 16), "transform: op %d lookup table not 16B aligned", o);
+        int64_t need = s.a0 * 16;
+        if (smem + need <= kXfSmemBudget) { d.smem_off = smem; smem += static_cast<int>(need); }
+        break;
+      }
+      case TXF_OP_FILL_I64: case TXF_OP_FILL_F32: case TXF_OP_FILL_STR: break;
+      case TXF_OP_RATIO_LABEL:
+        TXF_REQUIRE(s.in1 != nullptr && aligned(s.in1, 16), "transform: op %d (label) needs in1 (16B aligned)", o);
+        TXF_REQUIRE(s.in_dtype == TXF_F32, "transform: op %d (label) takes fp32 columns", o);
+        break;
+      default:
+        TXF_REQUIRE(false, "transform: op %d has unknown kind %d", o, s.kind);
+    }
+  }
+  prog.smem_bytes = smem;
+  if (smem > 48 * 1024)
+    TXF_CUDA(cudaFuncSetAttribute(transform_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  int64_t ntiles = (n + kXfTileRows - 1) / kXfTileRows;
+  int grid = static_cast<int>(ntiles < kSMs ? ntiles : kSMs);
+  transform_kernel<<<grid, kXfBlock, smem, static_cast<cudaStream_t>(stream)>>>(prog, n);
+  TXF_LAUNCH_CHECK();
+  count_launch(1);
+  g_last_grid = grid; g_last_block = kXfBlock; g_last_smem = smem;
+  return TXF_OK;
+}
+
+int txf_transform_launch_info(int* grid, int* block, int* smem_bytes) {
+  if (grid) *grid = txf::g_last_grid;
+  if (block) *block = txf::g_last_block;
+  if (smem_bytes) *smem_bytes = txf::g_last_smem;
+  return TXF_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,587 @@
+"""Host driver of the analyze + transform pass (the work tft_beam.AnalyzeAndTransformDataset does
+for ``preprocessing_fn``, ``airflow-dags/taxi_utils.py:106-145``).
+
+``Engine.analyze`` runs every analyzer of the plan in ONE pass over the rows held by this rank
+(moments, vocabulary counts, quantile bracket counts), merges the partial states across ranks
+with ``dist.Comm`` and finalises them on the GPU.  ``Engine.transform`` launches the single fused
+transform kernel.  All arithmetic happens in libtaxi_xf.so; PyTorch only owns the buffers and the
+stream, and there is no CPU fallback (``_native`` raises at import when the library is missing).
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional, Sequence, Tuple, Union
+
+import torch
+
+from . import _native as nat
+from .columns import NumericColumn, StringColumn, Table
+from .dist import Comm
+from .plan import BucketSpec, FillSpec, Plan, RatioLabelSpec, VocabSpec, ZScoreSpec
+
+EMPTY_VOCAB_SENTINEL = b"49d0cd50-04bb-48c0-bc6f-5b575dce351a"  # tft's placeholder for an empty vocabulary
+_DT = {"float32": nat.TXF_F32, "int64": nat.TXF_I64}
+
+
+def _pow2_at_least(x: int) -> int:
+    p = 1
+    while p < x:
+        p <<= 1
+    return p
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+@dataclass
+class VocabResult:
+    spec_key: Tuple
+    size: int                      # len(vocabulary) -- the real list length, not top_k
+    lookup: torch.Tensor           # uint8 bytes of the 16-byte-slot lookup table
+    lookup_cap: int
+    terms_offsets: torch.Tensor    # int32 [size+1] (device), id order
+    terms_pool: torch.Tensor       # uint8 (device)
+
+    def terms(self) -> List[bytes]:
+        o = self.terms_offsets.cpu().numpy()
+        buf = self.terms_pool[: int(o[-1])].cpu().numpy().tobytes()
+        return [buf[o[i]:o[i + 1]] for i in range(self.size)]
+
+
+@dataclass
+class BucketResult:
+    keys: List[str]
+    num_buckets: int
+    boundaries: torch.Tensor       # float32 [ncols, T] (device), first nbound[c] entries are valid
+    nbound: torch.Tensor           # int32 [ncols] (device)
+    path: str = "sample-select"
+
+    def boundaries_of(self, key: str):
+        c = self.keys.index(key)
+        return self.boundaries[c, : int(self.nbound[c].item())].cpu().numpy()
+
+
+@dataclass
+class TransformState:
+    """Analyzer results, device resident (what tft stores as constants of the transform graph)."""
+
+    plan: Plan
+    moment_keys: List[str]
+    mean_var: Optional[torch.Tensor]                     # float32 [n, 2] (device)
+    moments: Optional[torch.Tensor]                      # float64 [n, 3] (count, mean, M2) (device)
+    vocabs: Dict[Tuple, VocabResult] = field(default_factory=dict)
+    buckets: Dict[int, BucketResult] = field(default_factory=dict)
+    num_rows: int = 0
+
+    def mean_var_of(self, key: str):
+        return tuple(self.mean_var[self.moment_keys.index(key)].cpu().tolist())
+
+    def detach(self) -> "TransformState":
+        """Copy the state out of the Engine's reusable workspaces.  A state returned by
+        Engine.analyze aliases them and is overwritten by the next analyze() on that Engine."""
+        c = lambda t: None if t is None else t.clone()
+        return TransformState(
+            plan=self.plan, moment_keys=list(self.moment_keys), mean_var=c(self.mean_var), moments=c(self.moments),
+            vocabs={k: VocabResult(v.spec_key, v.size, v.lookup.clone(), v.lookup_cap, v.terms_offsets.clone(), v.terms_pool.clone())
+                    for k, v in self.vocabs.items()},
+            buckets={k: BucketResult(list(b.keys), b.num_buckets, b.boundaries.clone(), b.nbound.clone(), b.path)
+                     for k, b in self.buckets.items()},
+            num_rows=self.num_rows)
+
+
+def _vocab_key(s: VocabSpec) -> Tuple:
+    return (s.in_key, s.top_k, s.frequency_threshold)
+
+
+class Engine:
+    def __init__(self, plan: Plan, device: Union[str, torch.device] = "cuda", comm: Optional[Comm] = None,
+                 vocab_capacity: int = 1 << 16, arena_bytes: int = 1 << 22, sample_size: int = 1 << 21,
+                 bracket_sigmas: float = 5.0, seed: int = 20190501):
+        self.plan = plan
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError("Engine needs a CUDA device: the analyze/transform kernels have no CPU path")
+        self.comm = comm or Comm()
+        self.vocab_capacity = _pow2_at_least(vocab_capacity)
+        self.arena_bytes = int(arena_bytes)
+        self.sample_size = int(sample_size)
+        self.bracket_sigmas = float(bracket_sigmas)
+        self.seed = int(seed)
+        self._ws: Dict[Tuple, torch.Tensor] = {}
+        self.force_general_quantiles = False
+        self.last_quantile_path: Dict[int, str] = {}
+
+        self.moment_keys: List[str] = []
+        for s in plan.of(ZScoreSpec):
+            if s.in_key not in self.moment_keys:
+                self.moment_keys.append(s.in_key)
+        self.vocab_specs: Dict[Tuple, VocabSpec] = {}
+        for s in plan.of(VocabSpec):
+            if s.frequency_threshold is not None:
+                raise NotImplementedError("frequency_threshold is not supported yet")
+            self.vocab_specs.setdefault(_vocab_key(s), s)
+        self.bucket_groups: Dict[int, List[str]] = {}
+        for s in plan.of(BucketSpec):
+            keys = self.bucket_groups.setdefault(s.num_buckets, [])
+            if s.in_key not in keys:
+                keys.append(s.in_key)
+        for nb, keys in self.bucket_groups.items():
+            if len(keys) > nat.TXF_MAX_COLS:
+                raise NotImplementedError(f"at most {nat.TXF_MAX_COLS} bucketized features per num_buckets value")
+        if len(self.moment_keys) > nat.TXF_MAX_COLS:
+            raise NotImplementedError(f"at most {nat.TXF_MAX_COLS} z-scored features")
+
+    # ---- buffers ------------------------------------------------------------------------------
+    def _buf(self, name: str, shape, dtype, zero: bool = False) -> torch.Tensor:
+        """Workspace cached by (name, shape, dtype): repeated analyze/transform calls reuse it."""
+        shape = tuple(int(x) for x in (shape if isinstance(shape, (tuple, list)) else (shape,)))
+        key = (name, shape, dtype)
+        t = self._ws.get(key)
+        if t is None:
+            t = torch.zeros(shape, dtype=dtype, device=self.device) if zero else torch.empty(shape, dtype=dtype, device=self.device)
+            self._ws[key] = t
+        elif zero:
+            t.zero_()
+        return t
+
+    @staticmethod
+    def _stream() -> int:
+        return torch.cuda.current_stream().cuda_stream
+
+    def _check_table(self, t: Table):
+        if t.device.type != "cuda":
+            raise RuntimeError("kernels take GPU-resident tables: call table.to('cuda') first")
+        for k in self.plan.input_keys():
+            if k not in t:
+                raise KeyError(f"input feature {k!r} is missing from the table")
+            want = self.plan.schema[k]
+            if t[k].dtype != want:
+                raise TypeError(f"feature {k!r}: table has {t[k].dtype}, the plan was traced with {want}")
+
+    @staticmethod
+    def _num_args(cols: Sequence[NumericColumn]):
+        return (nat.ptr_array([c.values.data_ptr() for c in cols]), nat.ptr_array([_ptr(c.valid) for c in cols]),
+                nat.i32_array([_DT[c.dtype] for c in cols]))
+
+    # ---- analyze ------------------------------------------------------------------------------
+    def analyze(self, data: Union[Table, Sequence[Table]]) -> TransformState:
+        chunks = [data] if isinstance(data, Table) else list(data)
+        for c in chunks:
+            self._check_table(c)
+        n_local = sum(len(c) for c in chunks)
+        if self.comm.active:
+            nl = torch.tensor([n_local], dtype=torch.int64, device=self.device)
+            n_locals = [int(v) for v in self.comm.all_gather(nl).flatten().tolist()]
+        else:
+            n_locals = [n_local]
+        n_total = sum(n_locals)
+        state = TransformState(plan=self.plan, moment_keys=list(self.moment_keys), mean_var=None, moments=None, num_rows=n_total)
+
+        self._analyze_moments(chunks, state)
+        pending_q = {nb: self._quantiles_launch(nb, keys, chunks, n_locals) for nb, keys in self.bucket_groups.items()}
+        pending_v = {vk: self._vocab_count(vk, spec, chunks) for vk, spec in self.vocab_specs.items()}
+        # one host round trip: everything queued above has to finish before sizes/flags are read
+        torch.cuda.current_stream().synchronize()
+        for nb, pend in pending_q.items():
+            state.buckets[nb] = self._quantiles_finish(nb, pend, chunks, n_total)
+        for vk, pend in pending_v.items():
+            state.vocabs[vk] = self._vocab_finish(vk, self.vocab_specs[vk], pend)
+        return state
+
+    # -- moments
+    def _analyze_moments(self, chunks, state: TransformState):
+        nm = len(self.moment_keys)
+        if nm == 0:
+            return
+        s = self._stream()
+        mstate = self._buf("mom_state", (nm, 3), torch.float64, zero=True)
+        ws = self._buf("mom_ws", nat.query("txf_moments_workspace_bytes", nm), torch.uint8)
+        for ch in chunks:
+            if len(ch) == 0:
+                continue
+            v, m, d = self._num_args([ch[k] for k in self.moment_keys])
+            nat.call("txf_moments_update", v, m, d, nm, len(ch), mstate.data_ptr(), ws.data_ptr(), s)
+        if self.comm.active:
+            gathered = self.comm.all_gather(mstate)  # [W, nm, 3], rank order
+            nat.call("txf_moments_merge", gathered.data_ptr(), self.comm.world, nm, mstate.data_ptr(), s)
+        mv = self._buf("mean_var", (nm, 2), torch.float32)
+        nat.call("txf_moments_finalize", mstate.data_ptr(), nm, mv.data_ptr(), s)
+        state.moments, state.mean_var = mstate, mv
+
+    # -- exact multi-rank selection driver (general engine)
+    def _msel(self, name: str, ncols: int, R: int, ranks_dev: torch.Tensor, passes_fn, reduce: bool) -> torch.Tensor:
+        """ranks_dev: int64 [ncols, R] (device).  passes_fn(state_ptr, p) queues the histogram
+        launches of pass p.  Returns uint32-as-int32 keys [ncols, R]."""
+        s = self._stream()
+        st = self._buf(name + "_msel", nat.query("txf_msel_state_bytes", ncols, R), torch.uint8)
+        nat.call("txf_msel_begin", st.data_ptr(), ncols, R, ranks_dev.data_ptr(), s)
+        hist = st[: nat.query("txf_msel_hist_bytes", ncols, R)].view(torch.int64)
+        for p in range(4):
+            passes_fn(st.data_ptr(), p)
+            if reduce:
+                self.comm.all_reduce_sum_(hist)
+            nat.call("txf_msel_resolve", st.data_ptr(), ncols, R, p, s)
+        keys = self._buf(name + "_keys", (ncols, R), torch.int32)
+        nat.call("txf_msel_result", st.data_ptr(), ncols, R, keys.data_ptr(), s)
+        return keys
+
+    def _target_ranks(self, n_total: int, nb: int) -> List[int]:
+        return [min(max((i * n_total + nb - 1) // nb, 1), max(n_total, 1)) for i in range(1, nb)]
+
+    # -- quantiles
+    def _quantiles_launch(self, nb: int, keys: List[str], chunks, n_locals: List[int]):
+        """Queue the sample-select pipeline for one num_buckets group; returns what _finish needs."""
+        T = nb - 1
+        n_total = sum(n_locals)
+        n_local = n_locals[self.comm.rank]
+        ncols = len(keys)
+        pend = {"keys": keys, "T": T, "fast": False}
+        if T < 1 or n_total == 0:
+            return pend
+        M_total = min(self.sample_size, n_total // 8)
+        if self.force_general_quantiles or T > nat.TXF_QMAX_TARGETS or n_total < (1 << 18) or M_total < 1024 * T:
+            return pend
+        # per-rank sample sizes, proportional to the rows each rank holds (host arithmetic, no sync)
+        M_ranks = [(M_total * nl) // n_total for nl in n_locals]
+        M_sum = sum(M_ranks)
+        ranks = self._target_ranks(n_total, nb)
+        edges_ranks = []
+        for r in ranks:
+            q = r / n_total
+            k = min(max(math.ceil(q * M_sum), 1), M_sum)
+            d = int(math.ceil(self.bracket_sigmas * math.sqrt(M_sum * q * (1.0 - q)))) + 2
+            edges_ranks += [max(1, k - d), min(M_sum, k + d)]
+        if any(b < a for a, b in zip(edges_ranks, edges_ranks[1:])):
+            return pend  # brackets would overlap: too many targets for this sample
+        s = self._stream()
+        # (1) sample, chunk by chunk
+        M_local = M_ranks[self.comm.rank]
+        parts = []
+        left = M_local
+        for i, ch in enumerate(chunks):
+            m_c = left if i == len(chunks) - 1 else (M_local * len(ch)) // max(n_local, 1)
+            m_c = min(m_c, len(ch))
+            left -= m_c
+            if m_c <= 0:
+                continue
+            buf = self._buf(f"q{nb}_sample{i}", (ncols, m_c), torch.int32)
+            v, m, d = self._num_args([ch[k] for k in keys])
+            nat.call("txf_qsample", v, m, d, ncols, len(ch), m_c, self.seed + 7919 * i + 104729 * self.comm.rank, buf.data_ptr(), s)
+            parts.append(buf)
+        if parts:
+            sample = parts[0] if len(parts) == 1 else torch.cat(parts, dim=1)
+        else:
+            sample = torch.empty((ncols, 0), dtype=torch.int32, device=self.device)
+        M_have = sample.shape[1]
+        if self.comm.active:
+            Mmax = max(max(M_ranks), 1)
+            pad = self._buf(f"q{nb}_sample_pad", (ncols, Mmax), torch.int32, zero=True)
+            pad[:, :M_have] = sample
+            g = self.comm.all_gather(pad)  # [W, ncols, Mmax]
+            # ranks whose chunks could not supply their share contribute what they have; the
+            # order statistics below are taken over the slots every rank agreed on (host arithmetic)
+            sample = torch.cat([g[r, :, : M_ranks[r]] for r in range(self.comm.world)], dim=1).contiguous()
+            if M_have != M_local:
+                raise RuntimeError("sample size mismatch between chunks and plan")
+        sample = sample.contiguous()
+        M_sum = sample.shape[1]
+        # (2) bracket edges = exact order statistics of the sample
+        er = torch.tensor([edges_ranks] * ncols, dtype=torch.int64, device=self.device)
+        sptrs = nat.ptr_array([sample[c].data_ptr() for c in range(ncols)])
+
+        def sample_pass(st, p):
+            nat.call("txf_msel_hist", st, ncols, 2 * T, p, sptrs, None, None, 1, M_sum, None, s)
+
+        edges = self._msel(f"q{nb}_edges", ncols, 2 * T, er, sample_pass, reduce=False)
+        # (3) the one streaming pass over the column
+        cells = self._buf(f"q{nb}_cells", (ncols, 4 * T + 1), torch.int64, zero=True)
+        cand_cap = max(1 << 16, n_local // 8)
+        cand = self._buf(f"q{nb}_cand", (ncols, cand_cap), torch.int32)
+        cand_count = self._buf(f"q{nb}_cand_count", (ncols,), torch.int64, zero=True)
+        for ch in chunks:
+            if len(ch) == 0:
+                continue
+            v, m, d = self._num_args([ch[k] for k in keys])
+            nat.call("txf_qcount", v, m, d, ncols, len(ch), T, edges.data_ptr(), cells.data_ptr(), cand.data_ptr(),
+                     cand_count.data_ptr(), cand_cap, s)
+        pend.update(fast=True, edges=edges, cells=cells, cand=cand, cand_count=cand_count, cand_cap=cand_cap, ranks=ranks)
+        if not self.comm.active:
+            self._quantiles_resolve(nb, pend)
+        return pend
+
+    def _quantiles_resolve(self, nb: int, pend):
+        """cells/candidates (already merged across ranks) -> boundaries; all on the stream."""
+        keys, T = pend["keys"], pend["T"]
+        ncols = len(keys)
+        s = self._stream()
+        ranks_dev = torch.tensor(pend["ranks"], dtype=torch.int64, device=self.device)
+        direct = self._buf(f"q{nb}_direct", (ncols, T), torch.int32)
+        cand_rank = self._buf(f"q{nb}_cand_rank", (ncols, T), torch.int64)
+        status = self._buf(f"q{nb}_status", (ncols,), torch.int32)
+        cand, cand_count, cand_cap = pend["cand"], pend["cand_count"], pend["cand_cap"]
+        nat.call("txf_qresolve", pend["cells"].data_ptr(), pend["edges"].data_ptr(), cand_count.data_ptr(), cand_cap,
+                 ranks_dev.data_ptr(), ncols, T, direct.data_ptr(), cand_rank.data_ptr(), status.data_ptr(), s)
+        cptrs = nat.ptr_array([cand[c].data_ptr() for c in range(ncols)])
+
+        def cand_pass(st, p):
+            nat.call("txf_msel_hist", st, ncols, T, p, cptrs, None, None, 1, cand.shape[1], cand_count.data_ptr(), s)
+
+        sel = self._msel(f"q{nb}_sel", ncols, T, cand_rank, cand_pass, reduce=False)
+        bounds = self._buf(f"q{nb}_bounds", (ncols, T), torch.float32)
+        nbound = self._buf(f"q{nb}_nbound", (ncols,), torch.int32)
+        nat.call("txf_qfinal", direct.data_ptr(), cand_rank.data_ptr(), sel.data_ptr(), ncols, T, bounds.data_ptr(),
+                 nbound.data_ptr(), s)
+        pend.update(status=status, bounds=bounds, nbound=nbound)
+
+    def _quantiles_general(self, nb: int, keys: List[str], chunks, n_total: int) -> BucketResult:
+        """Exact radix select over the whole column (any number of boundaries)."""
+        T = nb - 1
+        ncols = len(keys)
+        s = self._stream()
+        ranks = self._target_ranks(n_total, nb)
+        rd = torch.tensor([ranks] * ncols, dtype=torch.int64, device=self.device)
+        args = [self._num_args([ch[k] for k in keys]) + (len(ch),) for ch in chunks if len(ch)]
+
+        def data_pass(st, p):
+            for v, m, d, n in args:
+                nat.call("txf_msel_hist", st, ncols, T, p, v, m, d, 0, n, None, s)
+
+        sel = self._msel(f"q{nb}_gen", ncols, T, rd, data_pass, reduce=self.comm.active)
+        bounds = self._buf(f"q{nb}_bounds", (ncols, T), torch.float32)
+        nbound = self._buf(f"q{nb}_nbound", (ncols,), torch.int32)
+        zeros = self._buf(f"q{nb}_direct", (ncols, T), torch.int32, zero=True)
+        nat.call("txf_qfinal", zeros.data_ptr(), rd.data_ptr(), sel.data_ptr(), ncols, T, bounds.data_ptr(), nbound.data_ptr(), s)
+        return BucketResult(list(keys), nb, bounds, nbound, path="radix-select")
+
+    def _quantiles_finish(self, nb: int, pend, chunks, n_total: int) -> BucketResult:
+        keys, T = pend["keys"], pend["T"]
+        ncols = len(keys)
+        if T < 1 or n_total == 0:
+            self.last_quantile_path[nb] = "empty"
+            return BucketResult(list(keys), nb, torch.zeros((ncols, max(T, 1)), dtype=torch.float32, device=self.device),
+                                torch.zeros((ncols,), dtype=torch.int32, device=self.device), path="empty")
+        if pend["fast"] and self.comm.active:
+            # merge per-rank cell counts (sum) and candidate keys (concatenation), then resolve
+            cc = pend["cand_count"].cpu().tolist()
+            overflow = torch.tensor([1 if max(cc) > pend["cand_cap"] else 0], dtype=torch.int64, device=self.device)
+            self.comm.all_reduce_max_(overflow)
+            self.comm.all_reduce_sum_(pend["cells"])
+            if int(overflow.item()) == 0:
+                merged = [self.comm.all_gather_var(pend["cand"][c], int(cc[c]))[0] for c in range(ncols)]
+                cap = max(max(int(m.numel()) for m in merged), 1)
+                cand = self._buf(f"q{nb}_cand_merged", (ncols, cap), torch.int32)
+                count = self._buf(f"q{nb}_cand_count_merged", (ncols,), torch.int64)
+                for c, m in enumerate(merged):
+                    cand[c, : m.numel()] = m
+                    count[c] = m.numel()
+                pend.update(cand=cand, cand_count=count, cand_cap=cap)
+                self._quantiles_resolve(nb, pend)
+            else:
+                pend["fast"] = False
+        if pend["fast"]:
+            status = pend["status"].cpu()
+            if int(status.abs().sum()) == 0:
+                self.last_quantile_path[nb] = "sample-select"
+                return BucketResult(list(keys), nb, pend["bounds"], pend["nbound"], path="sample-select")
+        self.last_quantile_path[nb] = "radix-select"
+        return self._quantiles_general(nb, keys, chunks, n_total)
+
+    # -- vocabulary
+    def _vocab_bufs(self, tag: str, capacity: int):
+        table = self._buf(f"{tag}_table", nat.query("txf_vocab_table_bytes", capacity), torch.uint8, zero=True)
+        arena = self._buf(f"{tag}_arena", self.arena_bytes, torch.uint8)
+        ctrl = self._buf(f"{tag}_ctrl", 8, torch.int64, zero=True)
+        ent = self._buf(f"{tag}_ent", capacity, torch.int32)
+        counts = self._buf(f"{tag}_counts", capacity, torch.int32)
+        return table, arena, ctrl, ent, counts
+
+    def _vocab_count(self, vk: Tuple, spec: VocabSpec, chunks):
+        s = self._stream()
+        tag = f"v_{spec.in_key}_{spec.top_k}"
+        cap = self.vocab_capacity
+        table, arena, ctrl, ent, counts = self._vocab_bufs(tag, cap)
+        for ch in chunks:
+            if len(ch) == 0:
+                continue
+            col: StringColumn = ch[spec.in_key]
+            nat.call("txf_vocab_count", col.offsets.data_ptr(), col.pool.data_ptr(), _ptr(col.valid), len(ch), table.data_ptr(),
+                     cap, arena.data_ptr(), self.arena_bytes, ctrl.data_ptr(), s)
+        nat.call("txf_vocab_compact", table.data_ptr(), cap, arena.data_ptr(), ent.data_ptr(), counts.data_ptr(), ctrl.data_ptr(), s)
+        return dict(tag=tag, cap=cap, table=table, arena=arena, ctrl=ctrl, ent=ent, counts=counts)
+
+    def _check_vocab_ctrl(self, ctrl_host, spec: VocabSpec):
+        if int(ctrl_host[2]) & 2:
+            raise nat.NativeError(
+                f"vocabulary table for {spec.in_key!r} is full ({self.vocab_capacity} slots): raise Engine(vocab_capacity=...)")
+        if int(ctrl_host[2]) & 1:
+            raise nat.NativeError(
+                f"vocabulary arena for {spec.in_key!r} is full ({self.arena_bytes} bytes): raise Engine(arena_bytes=...)")
+        if int(ctrl_host[1]) * 4 > self.vocab_capacity * 3:
+            raise nat.NativeError(
+                f"vocabulary table for {spec.in_key!r} is over 75% full: raise Engine(vocab_capacity=...)")
+
+    def _export_entries(self, pend, ent: torch.Tensor, m: int):
+        """(fp, tag, count, offsets int64 [m+1], pool) of the m listed entries, on the device."""
+        s = self._stream()
+        tag = pend["tag"]
+        fp = self._buf(f"{tag}_x_fp", max(m, 1), torch.int64)
+        tg = self._buf(f"{tag}_x_tag", max(m, 1), torch.int64)
+        cnt = self._buf(f"{tag}_x_cnt", max(m, 1), torch.int64)
+        ln = self._buf(f"{tag}_x_len", max(m, 1), torch.int32)
+        nat.call("txf_vocab_export_meta", pend["table"].data_ptr(), ent.data_ptr(), m, fp.data_ptr(), tg.data_ptr(), cnt.data_ptr(),
+                 ln.data_ptr(), s)
+        offsets = torch.zeros(m + 1, dtype=torch.int64, device=self.device)
+        if m:
+            torch.cumsum(ln[:m].to(torch.int64), 0, out=offsets[1:])
+        pool = self._buf(f"{tag}_x_pool", self.arena_bytes + nat.TXF_POOL_SLACK, torch.uint8)
+        nat.call("txf_vocab_export_bytes", pend["table"].data_ptr(), pend["arena"].data_ptr(), ent.data_ptr(), m, offsets.data_ptr(),
+                 pool.data_ptr(), s)
+        return fp, tg, cnt, offsets, pool
+
+    def _vocab_finish(self, vk: Tuple, spec: VocabSpec, pend) -> VocabResult:
+        s = self._stream()
+        ctrl_host = pend["ctrl"].cpu().tolist()
+        self._check_vocab_ctrl(ctrl_host, spec)
+        kept = int(ctrl_host[3])
+        if self.comm.active:
+            # exchange the admitted entries of every rank and rebuild one merged table everywhere
+            fp, tg, cnt, offsets, pool = self._export_entries(pend, pend["ent"], kept)
+            nbytes = int(offsets[-1].item())
+            g_fp, counts = self.comm.all_gather_var(fp, kept)
+            g_tg, _ = self.comm.all_gather_var(tg, kept)
+            g_cnt, _ = self.comm.all_gather_var(cnt, kept)
+            lens = (offsets[1:] - offsets[:-1]).contiguous() if kept else torch.zeros(0, dtype=torch.int64, device=self.device)
+            g_len, _ = self.comm.all_gather_var(lens, kept)
+            g_pool, _ = self.comm.all_gather_var(pool, nbytes)
+            m = int(g_fp.numel())
+            g_off = torch.zeros(m + 1, dtype=torch.int64, device=self.device)
+            if m:
+                torch.cumsum(g_len, 0, out=g_off[1:])
+            g_pool = torch.cat([g_pool, torch.zeros(nat.TXF_POOL_SLACK, dtype=torch.uint8, device=self.device)])
+            cap2 = max(self.vocab_capacity, _pow2_at_least(2 * max(m, 1)))
+            tag2 = pend["tag"] + "_merged"
+            table, arena, ctrl, ent, counts_buf = self._vocab_bufs(tag2, cap2)
+            nat.call("txf_vocab_insert", g_fp.data_ptr(), g_tg.data_ptr(), g_cnt.data_ptr(), g_off.data_ptr(), g_pool.data_ptr(), m,
+                     table.data_ptr(), cap2, arena.data_ptr(), self.arena_bytes, ctrl.data_ptr(), s)
+            nat.call("txf_vocab_compact", table.data_ptr(), cap2, arena.data_ptr(), ent.data_ptr(), counts_buf.data_ptr(),
+                     ctrl.data_ptr(), s)
+            pend = dict(tag=tag2, cap=cap2, table=table, arena=arena, ctrl=ctrl, ent=ent, counts=counts_buf)
+            ctrl_host = ctrl.cpu().tolist()
+            if int(ctrl_host[2]):
+                raise nat.NativeError(f"merged vocabulary table/arena for {spec.in_key!r} overflowed")
+            kept = int(ctrl_host[3])
+        tag, table, arena, ctrl, ent, counts = (pend[k] for k in ("tag", "table", "arena", "ctrl", "ent", "counts"))
+        k = kept if spec.top_k is None else min(spec.top_k, kept)
+        sel, m = ent, kept
+        if kept > k:
+            # count cut-off: the k-th largest count (exact), then only entries >= it need ordering
+            rank = torch.tensor([[kept - k + 1]], dtype=torch.int64, device=self.device)
+            cptr = nat.ptr_array([counts.data_ptr()])
+
+            def count_pass(st, p):
+                nat.call("txf_msel_hist", st, 1, 1, p, cptr, None, None, 1, kept, None, s)
+
+            thr = self._msel(f"{tag}_thr", 1, 1, rank, count_pass, reduce=False)
+            sel = self._buf(f"{tag}_sel", pend["cap"], torch.int32)
+            nat.call("txf_vocab_filter_ge", ent.data_ptr(), counts.data_ptr(), kept, thr.data_ptr(), sel.data_ptr(), ctrl.data_ptr(), s)
+            m = int(ctrl[5].item())
+        scratch = self._buf(f"{tag}_sort", max(nat.query("txf_vocab_sort_scratch_bytes", m), 16), torch.uint8)
+        nat.call("txf_vocab_sort", table.data_ptr(), arena.data_ptr(), sel.data_ptr(), m, scratch.data_ptr(), s)
+        lookup_cap = _pow2_at_least(max(2 * (spec.top_k if spec.top_k is not None else k), 2 * k, 2))
+        lookup = self._buf(f"{tag}_lookup", nat.query("txf_vocab_lookup_bytes", lookup_cap), torch.uint8)
+        if k == 0:
+            return self._vocab_from_terms(vk, [EMPTY_VOCAB_SENTINEL], lookup, lookup_cap)
+        nat.call("txf_vocab_build_lookup", table.data_ptr(), sel.data_ptr(), k, lookup.data_ptr(), lookup_cap, s)
+        _, _, _, offsets, pool = self._export_entries(pend, sel, k)
+        return VocabResult(vk, k, lookup, lookup_cap, offsets.to(torch.int32), pool)
+
+    def _vocab_from_terms(self, vk: Tuple, terms: List[bytes], lookup: Optional[torch.Tensor] = None,
+                          lookup_cap: Optional[int] = None) -> VocabResult:
+        col = StringColumn.from_list(terms).to(self.device)
+        k = len(terms)
+        if lookup is None:
+            lookup_cap = _pow2_at_least(max(2 * k, 2))
+            lookup = torch.empty(nat.query("txf_vocab_lookup_bytes", lookup_cap), dtype=torch.uint8, device=self.device)
+        nat.call("txf_vocab_lookup_from_terms", col.offsets.data_ptr(), col.pool.data_ptr(), k, lookup.data_ptr(), lookup_cap,
+                 self._stream())
+        return VocabResult(vk, k, lookup, lookup_cap, col.offsets, col.pool)
+
+    # ---- transform ----------------------------------------------------------------------------
+    def transform(self, table: Table, state: TransformState, out: Optional[Table] = None) -> Table:
+        """Launch the fused transform kernel over one GPU-resident chunk; returns the output table
+        (reusing `out`'s buffers when given)."""
+        self._check_table(table)
+        n = len(table)
+        dev = self.device
+        ops = (nat.TxfOp * len(self.plan.specs))()
+        cols: Dict[str, object] = {}
+        copies = []
+        for i, spec in enumerate(self.plan.specs):
+            op = ops[i]
+            prev = out[spec.out_key] if out is not None else None
+            if isinstance(spec, RatioLabelSpec):
+                fare, tips = table[spec.fare_key], table[spec.tips_key]
+                o = prev.values if prev is not None else torch.empty(n, dtype=torch.int64, device=dev)
+                op.kind, op.in_dtype = nat.OP_RATIO_LABEL, nat.TXF_F32
+                op.in0, op.valid0, op.in1, op.valid1 = fare.values.data_ptr(), _ptr(fare.valid), tips.values.data_ptr(), _ptr(tips.valid)
+                op.f0 = spec.ratio
+                op.out = o.data_ptr()
+                cols[spec.out_key] = NumericColumn(o)
+                continue
+            col = table[spec.in_key]
+            if isinstance(spec, ZScoreSpec):
+                o = prev.values if prev is not None else torch.empty(n, dtype=torch.float32, device=dev)
+                op.kind, op.in_dtype = nat.OP_ZSCORE, _DT[col.dtype]
+                op.in0, op.valid0 = col.values.data_ptr(), _ptr(col.valid)
+                op.p0 = state.mean_var[state.moment_keys.index(spec.in_key)].data_ptr()
+                cols[spec.out_key] = NumericColumn(o)
+            elif isinstance(spec, BucketSpec):
+                res = state.buckets[spec.num_buckets]
+                c = res.keys.index(spec.in_key)
+                o = prev.values if prev is not None else torch.empty(n, dtype=torch.int64, device=dev)
+                op.kind, op.in_dtype = nat.OP_BUCKETIZE, _DT[col.dtype]
+                op.in0, op.valid0 = col.values.data_ptr(), _ptr(col.valid)
+                op.p0, op.p1, op.a0 = res.boundaries[c].data_ptr(), res.nbound[c].data_ptr(), res.boundaries.shape[1]
+                cols[spec.out_key] = NumericColumn(o)
+            elif isinstance(spec, VocabSpec):
+                res = state.vocabs[_vocab_key(spec)]
+                o = prev.values if prev is not None else torch.empty(n, dtype=torch.int64, device=dev)
+                op.kind = nat.OP_VOCAB
+                op.in0, op.valid0, op.pool = col.offsets.data_ptr(), _ptr(col.valid), col.pool.data_ptr()
+                op.p0, op.a0, op.a1, op.a2, op.a3 = res.lookup.data_ptr(), res.lookup_cap, res.size, spec.num_oov_buckets, spec.default_value
+                cols[spec.out_key] = NumericColumn(o)
+            elif isinstance(spec, FillSpec):
+                if col.kind == "string":
+                    if prev is not None:
+                        o_off, o_pool = prev.offsets, prev.pool
+                    else:
+                        o_off = torch.empty(n + 1, dtype=torch.int32, device=dev) if n else torch.zeros(1, dtype=torch.int32, device=dev)
+                        o_pool = torch.empty(col.pool_bytes + nat.TXF_POOL_SLACK, dtype=torch.uint8, device=dev)
+                    op.kind = nat.OP_FILL_STR
+                    op.in0 = col.offsets.data_ptr()
+                    op.out = o_off.data_ptr()
+                    copies.append((o_pool, col))
+                    cols[spec.out_key] = StringColumn(o_off, o_pool, None, col.pool_bytes)
+                    continue
+                o = prev.values if prev is not None else torch.empty(n, dtype=col.values.dtype, device=dev)
+                op.kind = nat.OP_FILL_F32 if col.dtype == "float32" else nat.OP_FILL_I64
+                op.in_dtype = _DT[col.dtype]
+                op.in0, op.valid0 = col.values.data_ptr(), _ptr(col.valid)
+                cols[spec.out_key] = NumericColumn(o)
+            else:  # pragma: no cover
+                raise AssertionError(spec)
+            op.out = o.data_ptr()
+        if n:
+            nat.call("txf_transform", ops, len(self.plan.specs), n, self._stream())
+            for o_pool, col in copies:  # bytes of pass-through string features: plain device copy
+                if col.pool_bytes:
+                    o_pool[: col.pool_bytes].copy_(col.pool[: col.pool_bytes], non_blocking=True)
+        return Table(cols)
+
+    def analyze_and_transform(self, data: Union[Table, Sequence[Table]]):
+        chunks = [data] if isinstance(data, Table) else list(data)
+        state = self.analyze(chunks)
+        outs = [self.transform(c, state) for c in chunks]
+        return (outs[0] if isinstance(data, Table) else outs), state
