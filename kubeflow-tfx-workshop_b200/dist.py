@@ -39,9 +39,10 @@ class Comm:
         """-> [world, *t.shape], rank order."""
         if not self.active:
             return t.unsqueeze(0)
-        out = torch.empty((self.world,) + tuple(t.shape), dtype=t.dtype, device=t.device)
-        dist.all_gather_into_tensor(out, t.contiguous(), group=self.group)
-        return out
+        t = t.contiguous()
+        out = torch.empty((self.world * t.shape[0],) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+        dist.all_gather_into_tensor(out, t, group=self.group)
+        return out.view((self.world,) + tuple(t.shape))
 
     def all_reduce_sum_(self, t: torch.Tensor) -> torch.Tensor:
         if self.active:

@@ -1,0 +1,367 @@
+"""GPU parity tests (-m gpu): the CUDA path, called through the C ABI, against the oracle."""
+import numpy as np
+import pytest
+import torch
+
+import helpers
+from helpers import O
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ktw():
+    import kubeflow_tfx_workshop_b200 as k
+    assert torch.cuda.is_available()
+    return k
+
+
+@pytest.fixture(scope="module")
+def fn(ktw):
+    return helpers.load_example_preprocessing_fn(ktw).preprocessing_fn
+
+
+def check_outputs(out, want, wstate):
+    for key, w in want.items():
+        col = out[key]
+        if isinstance(w, list):
+            assert col.to_list() == w, key
+        elif w.dtype == np.float32:
+            mean, var = wstate["zscore"][key[:-3]]
+            got = col.values.cpu().numpy()
+            assert helpers.zscore_close(got, w, mean, var), (key, np.abs(got - w).max())
+        else:
+            got = col.values.cpu().numpy()
+            assert got.dtype == w.dtype and np.array_equal(got, w), (key, int((got != w).sum()))
+
+
+def check_state(state, wstate, exact_moments=False):
+    for k, (mean, var) in wstate["zscore"].items():
+        m, v = state.mean_var_of(k)
+        assert abs(m - float(mean)) <= 1e-6 * abs(float(mean)) + 1e-30, (k, m, mean)
+        assert abs(v - float(var)) <= 1e-6 * abs(float(var)) + 1e-30, (k, v, var)
+    for key, res in state.vocabs.items():
+        assert res.terms() == wstate["vocab"][key[0]], key
+    for nb, res in state.buckets.items():
+        for k in res.keys:
+            got = res.boundaries_of(k)
+            want = wstate["boundaries"][k]
+            assert got.dtype == np.float32 and np.array_equal(got.view(np.uint32), np.asarray(want, np.float32).view(np.uint32)), (k, got, want)
+
+
+# ------------------------------------------------------------------------------------------------
+# FarmHash on the device
+# ------------------------------------------------------------------------------------------------
+def test_fingerprint64_device_matches_oracle(ktw):
+    import json, os
+    nat = ktw._native
+    with open(os.path.join(helpers.GOLDEN, "farmhash_vectors.json")) as f:
+        gold = json.load(f)
+    items = [(bytes.fromhex(v["hex"]), int(v["fp"])) for v in gold["abseil_le32"] + gold["survey_gt32"]]
+    items += [(k.encode(), int(v)) for k, v in gold["tf_kat"]["full"].items()]
+    rng = np.random.default_rng(7)
+    extra = [bytes(rng.integers(0, 256, n, dtype=np.uint8)) for n in list(range(0, 200)) + [255, 256, 257, 1000, 4097]]
+    items += [(s, O.fingerprint64_c(s)) for s in extra]
+    col = ktw.StringColumn.from_list([s for s, _ in items]).to("cuda")
+    out = torch.empty(len(items), dtype=torch.int64, device="cuda")
+    nat.call("txf_fingerprint64_batch", col.offsets.data_ptr(), col.pool.data_ptr(), len(items), out.data_ptr(), None)
+    got = out.cpu().numpy().view(np.uint64)
+    want = np.array([fp for _, fp in items], np.uint64)
+    bad = np.nonzero(got != want)[0]
+    assert bad.size == 0, [(len(items[i][0]), int(got[i]), int(want[i])) for i in bad[:5]]
+
+
+# ------------------------------------------------------------------------------------------------
+# config 1: the bundled 15 000 rows
+# ------------------------------------------------------------------------------------------------
+def test_taxi_golden_15000(ktw, fn):
+    cols, want, wstate = helpers.load_taxi_golden()
+    host = helpers.table_from_oracle(cols, ktw)
+    plan = ktw.trace(fn, host.schema())
+    eng = ktw.Engine(plan)
+    out, state = eng.analyze_and_transform(host.to("cuda"))
+    check_state(state, wstate)
+    check_outputs(out, want, wstate)
+    # anchors stated in SURVEY.md Appendix B
+    assert int(out["tips_xf"].values.sum()) == 3382
+    assert state.vocabs[("company", 1000, None)].size == 61 and state.vocabs[("payment_type", 1000, None)].size == 7
+    assert int(out["company_xf"].values[3]) == 64
+
+
+def test_taxi_golden_through_tft_beam_api(ktw, fn):
+    """Same result through the reference-facing driver (notebooks/06_...:236-262 shape)."""
+    cols, want, wstate = helpers.load_taxi_golden()
+    host = helpers.table_from_oracle(cols, ktw)
+    meta = ktw.tf_metadata.DatasetMetadata(ktw.tf_metadata.Schema(host.schema()))
+    with ktw.tft_beam.Context(temp_dir="/tmp/unused"):
+        (transformed, tmeta), transform_fn = (host, meta) | ktw.tft_beam.AnalyzeAndTransformDataset(fn)
+    check_outputs(transformed, want, wstate)
+    assert tmeta.schema.column_dtypes["company_xf"] == "int64"
+    # TransformDataset on a second dataset re-applies the saved state (03a notebook :468)
+    sub = {k: O.NumCol(c.values[:4096], c.valid[:4096]) if isinstance(c, O.NumCol) else c.slice(0, 4096) for k, c in cols.items()}
+    first = helpers.table_from_oracle(sub, ktw)
+    out2, _ = ((first, meta), transform_fn) | ktw.tft_beam.TransformDataset()
+    check_outputs(out2, {k: (v[:4096]) for k, v in want.items()}, wstate)
+
+
+def test_state_save_load_roundtrip(ktw, fn, tmp_path):
+    cols, want, wstate = helpers.load_taxi_golden()
+    host = helpers.table_from_oracle(cols, ktw)
+    eng = ktw.Engine(ktw.trace(fn, host.schema()))
+    dev = host.to("cuda")
+    state = eng.analyze(dev)
+    ktw.save_state(state, str(tmp_path / "tfn"))
+    with open(tmp_path / "tfn" / "company.top1000.thrNone.vocab", "rb") as f:
+        assert f.read().split(b"\n")[:-1] == wstate["vocab"]["company"]
+    eng2, state2 = ktw.load_state(str(tmp_path / "tfn"))
+    check_outputs(eng2.transform(dev, state2), want, wstate)
+
+
+# ------------------------------------------------------------------------------------------------
+# synthetic taxi rows, both quantile engines, ragged sizes
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("n,force_general", [(300_001, False), (300_001, True), (1_000_003, False), (4099, False), (7, False), (1, False)])
+def test_synthetic_taxi(ktw, fn, n, force_general):
+    from kubeflow_tfx_workshop_b200 import synth
+    host = synth.taxi_table(n, backend="numpy")
+    eng = ktw.Engine(ktw.trace(fn, synth.TAXI_SCHEMA))
+    eng.force_general_quantiles = force_general
+    out, state = eng.analyze_and_transform(host.to("cuda"))
+    want, wstate = O.analyze_and_transform(helpers.oracle_from_table(host))
+    if n >= (1 << 18) and not force_general:
+        assert eng.last_quantile_path[10] == "sample-select"
+    else:
+        assert eng.last_quantile_path[10] == "radix-select"
+    check_state(state, wstate)
+    check_outputs(out, want, wstate)
+
+
+def test_synthetic_generators_agree_on_gpu(ktw):
+    """torch-on-GPU generator == numpy twin, bit for bit (the benchmark relies on it)."""
+    from kubeflow_tfx_workshop_b200 import synth
+    a = synth.taxi_table(50_001, backend="numpy")
+    b = synth.taxi_table(50_001, backend="torch", device="cuda")
+    for k in a.keys():
+        ca, cb = a[k], b[k]
+        if ca.kind == "string":
+            assert torch.equal(ca.offsets, cb.offsets.cpu()) and torch.equal(ca.pool, cb.pool.cpu()), k
+        else:
+            va, vb = ca.values, cb.values.cpu()
+            assert torch.equal(va.view(torch.int32) if va.dtype == torch.float32 else va,
+                               vb.view(torch.int32) if vb.dtype == torch.float32 else vb), k
+        assert (ca.valid is None) == (cb.valid is None) and (ca.valid is None or torch.equal(ca.valid, cb.valid.cpu())), k
+
+
+def test_chunked_analyze_equals_whole(ktw, fn):
+    """Analyzer state accumulates over chunks: two chunks == one table (exact for vocab/boundaries)."""
+    from kubeflow_tfx_workshop_b200 import synth
+    n1, n2 = 200_000, 150_003
+    c1 = synth.taxi_table(n1, 0, backend="numpy")
+    c2 = synth.taxi_table(n2, n1, backend="numpy")
+    whole = synth.taxi_table(n1 + n2, backend="numpy")
+    eng = ktw.Engine(ktw.trace(fn, synth.TAXI_SCHEMA))
+    state = eng.analyze([c1.to("cuda"), c2.to("cuda")]).detach()
+    want, wstate = O.analyze_and_transform(helpers.oracle_from_table(whole))
+    check_state(state, wstate)
+    out2 = eng.transform(c2.to("cuda"), state)
+    check_outputs(out2, {k: v[n1:] for k, v in want.items()}, wstate)
+
+
+# ------------------------------------------------------------------------------------------------
+# quantiles: config 5 style stress
+# ------------------------------------------------------------------------------------------------
+def _bucket_fn(ktw, keys, nb):
+    tf, tft = ktw.tf, ktw.tft
+
+    def f(inputs):
+        def dense(x):
+            return tf.squeeze(tf.sparse.to_dense(tf.SparseTensor(x.indices, x.values, [x.dense_shape[0], 1]), 0), axis=1)
+        return {k + "_b": tft.bucketize(dense(inputs[k]), nb) for k in keys}
+    return f
+
+
+@pytest.mark.parametrize("nb", [2, 3, 10, 33, 65, 100, 1000])
+def test_bucketize_stress(ktw, nb):
+    rng = np.random.default_rng(nb)
+    n = 400_003
+    cent = rng.normal(41.8, 0.1, 300).astype(np.float32)
+    data = {
+        "centroid": cent[(rng.integers(0, 300, n) * rng.integers(0, 300, n)) // 300],
+        "atom0": np.where(rng.random(n) < 0.4, 0.0, rng.normal(0, 1, n)).astype(np.float32),
+        "fine": rng.normal(-87.6, 0.05, n).astype(np.float32),
+        "uniform": rng.random(n).astype(np.float32),
+        "const": np.full(n, 3.25, np.float32),
+        "signed": (rng.standard_cauchy(n) * 10).astype(np.float32),
+        "ints": rng.integers(-50, 50, n).astype(np.int64),
+        "tiny": (rng.random(n) * 1e-40).astype(np.float32),  # denormals and +-0
+    }
+    data["tiny"][::7] = -0.0
+    valid = {"fine": rng.random(n) > 0.03}
+    cols = {k: O.NumCol(v, valid.get(k)) for k, v in data.items()}
+    host = helpers.table_from_oracle(cols, ktw)
+    keys = list(data)
+    eng = ktw.Engine(ktw.trace(_bucket_fn(ktw, keys, nb), host.schema()))
+    dev = host.to("cuda")
+    out, state = eng.analyze_and_transform(dev)
+    res = state.buckets[nb]
+    if nb <= 33:
+        assert eng.last_quantile_path[nb] == "sample-select"
+    if nb >= 100:
+        assert eng.last_quantile_path[nb] == "radix-select"
+    for k in keys:
+        filled = O.fill_in_missing(cols[k])
+        want_b = O.quantile_boundaries(filled, nb)
+        got_b = res.boundaries_of(k)
+        assert np.array_equal(got_b.view(np.uint32), want_b.view(np.uint32)), (k, nb, got_b[:5], want_b[:5])
+        assert np.array_equal(out[k + "_b"].values.cpu().numpy(), O.bucketize(filled, want_b)), (k, nb)
+    # the general engine returns the same boundaries
+    eng.force_general_quantiles = True
+    state2 = eng.analyze(dev)
+    for k in keys:
+        assert np.array_equal(state2.buckets[nb].boundaries_of(k).view(np.uint32), O.quantile_boundaries(O.fill_in_missing(cols[k]), nb).view(np.uint32)), k
+
+
+def test_bucketize_nan_goes_last(ktw):
+    x = np.array([0.5, np.nan, -1.0, 2.0, np.nan, 0.25, 1.0, 3.0] * 8, np.float32)
+    cols = {"x": O.NumCol(x)}
+    host = helpers.table_from_oracle(cols, ktw)
+    eng = ktw.Engine(ktw.trace(_bucket_fn(ktw, ["x"], 4), host.schema()))
+    out, state = eng.analyze_and_transform(host.to("cuda"))
+    want_b = O.quantile_boundaries(x, 4)
+    got_b = state.buckets[4].boundaries_of("x")
+    assert np.array_equal(got_b, want_b, equal_nan=True)
+    assert np.array_equal(out["x_b"].values.cpu().numpy(), O.bucketize(x, want_b))
+
+
+# ------------------------------------------------------------------------------------------------
+# vocabulary: config 4 style stress
+# ------------------------------------------------------------------------------------------------
+def _vocab_fn(ktw, key, top_k, oov, default_value=-1):
+    tf, tft = ktw.tf, ktw.tft
+
+    def f(inputs):
+        x = inputs[key]
+        d = tf.squeeze(tf.sparse.to_dense(tf.SparseTensor(x.indices, x.values, [x.dense_shape[0], 1]), ""), axis=1)
+        return {key + "_id": tft.compute_and_apply_vocabulary(d, top_k=top_k, num_oov_buckets=oov, default_value=default_value)}
+    return f
+
+
+def _stress_terms(n_distinct, rng):
+    """Distinct byte strings covering every FarmHash length class, with awkward bytes."""
+    terms = set()
+    lens = [1, 2, 3, 4, 7, 8, 15, 16, 17, 31, 32, 33, 63, 64, 65, 127, 128, 129, 300]
+    i = 0
+    while len(terms) < n_distinct:
+        L = lens[i % len(lens)] if i < 4 * len(lens) else int(rng.integers(1, 48))
+        t = bytes(rng.integers(1, 256, L, dtype=np.uint8))
+        terms.add(t)
+        i += 1
+    terms = list(terms)
+    terms[0] = b"has\nnewline"   # never admitted
+    terms[1] = b"has\rreturn"    # never admitted
+    terms[2] = b"ab"
+    terms[3] = b"ab\x00"         # prefix ordering with an embedded NUL
+    terms[4] = b"ab\x00\x00"
+    return terms
+
+
+@pytest.mark.parametrize("n_distinct,top_k,oov", [(50, 1000, 10), (3000, 1000, 10), (3000, 7, 3), (20000, 1000, 10), (20000, None, 0), (5000, 100, 70000)])
+def test_vocabulary_stress(ktw, n_distinct, top_k, oov):
+    rng = np.random.default_rng(n_distinct + (top_k or 0))
+    terms = _stress_terms(n_distinct, rng)
+    # constructed multiplicities: a long run of equal counts straddles the top_k cut-off
+    counts = np.maximum(1, (n_distinct // (np.arange(n_distinct) + 1)) // 8).astype(np.int64)
+    counts[:5] = [900, 800, 5, 5, 5]
+    rows = np.repeat(np.arange(n_distinct), counts)
+    rng.shuffle(rows)
+    items = [terms[i] for i in rows]
+    missing = rng.random(len(items)) < 0.1
+    items = [None if m else t for t, m in zip(items, missing)]
+    items[5] = b""  # a present-but-empty value behaves like a missing one
+    col = O.StrCol.from_list(items)
+    host = helpers.table_from_oracle({"s": col}, ktw)
+    eng = ktw.Engine(ktw.trace(_vocab_fn(ktw, "s", top_k, oov), host.schema()), vocab_capacity=1 << 17, arena_bytes=1 << 23)
+    out, state = eng.analyze_and_transform(host.to("cuda"))
+    filled = O.fill_in_missing(col)
+    want_vocab = O.finalize_vocabulary(O.vocab_counts(filled), top_k=top_k)
+    got_vocab = state.vocabs[("s", top_k, None)].terms()
+    assert got_vocab == want_vocab, next((i, a, b) for i, (a, b) in enumerate(zip(got_vocab, want_vocab)) if a != b)
+    want_ids = O.apply_vocabulary(filled, want_vocab, oov)
+    assert np.array_equal(out["s_id"].values.cpu().numpy(), want_ids)
+
+
+def test_vocabulary_empty_and_all_missing(ktw):
+    col = O.StrCol.from_list([None, b"", None, b"\n", None])
+    host = helpers.table_from_oracle({"s": col}, ktw)
+    eng = ktw.Engine(ktw.trace(_vocab_fn(ktw, "s", 10, 4), host.schema()))
+    out, state = eng.analyze_and_transform(host.to("cuda"))
+    filled = O.fill_in_missing(col)
+    want_vocab = O.finalize_vocabulary(O.vocab_counts(filled), top_k=10)
+    assert want_vocab == [O.EMPTY_VOCAB_SENTINEL]
+    assert state.vocabs[("s", 10, None)].terms() == want_vocab
+    assert np.array_equal(out["s_id"].values.cpu().numpy(), O.apply_vocabulary(filled, want_vocab, 4))
+
+
+# ------------------------------------------------------------------------------------------------
+# edge cases of the element-wise ops
+# ------------------------------------------------------------------------------------------------
+def test_label_nan_fare_and_fp32_threshold(ktw, fn):
+    """NaN fare -> 0; the threshold is the fp32 product fare * 0.2f (63 of the bundled rows differ
+    from an fp64 threshold)."""
+    from kubeflow_tfx_workshop_b200 import synth
+    host = synth.taxi_table(64, backend="numpy")
+    fare = host["fare"].values
+    fare[:6] = torch.tensor([float("nan"), 5.0, 10.0, 0.0, float("inf"), 27.05])
+    host["tips"].values[:6] = torch.tensor([1.0, 1.0, 2.0000002, 0.0, 1.0, 5.41])
+    eng = ktw.Engine(ktw.trace(fn, synth.TAXI_SCHEMA))
+    out, _ = eng.analyze_and_transform(host.to("cuda"))
+    want = O.tips_label(O.fill_in_missing(O.NumCol(fare.numpy())), O.fill_in_missing(O.NumCol(host["tips"].values.numpy())))
+    assert np.array_equal(out["tips_xf"].values.cpu().numpy(), want)
+    assert int(want[0]) == 0
+
+
+def test_zscore_constant_column_and_missing(ktw):
+    tf, tft = ktw.tf, ktw.tft
+
+    def f(inputs):
+        def dense(x):
+            return tf.squeeze(tf.sparse.to_dense(tf.SparseTensor(x.indices, x.values, [x.dense_shape[0], 1]), 0), axis=1)
+        return {k + "_z": tft.scale_to_z_score(dense(inputs[k])) for k in ("const", "holes", "big")}
+
+    n = 10_007
+    rng = np.random.default_rng(3)
+    cols = {"const": O.NumCol(np.full(n, 7.5, np.float32)),
+            "holes": O.NumCol(rng.normal(100, 3, n).astype(np.float32), rng.random(n) > 0.5),
+            "big": O.NumCol(rng.integers(0, 1 << 23, n).astype(np.int64), rng.random(n) > 0.01)}
+    host = helpers.table_from_oracle(cols, ktw)
+    eng = ktw.Engine(ktw.trace(f, host.schema()))
+    out, state = eng.analyze_and_transform(host.to("cuda"))
+    for k, c in cols.items():
+        filled = O.fill_in_missing(c)
+        mean, var = O.finalize_moments(O.moments(filled))
+        want = O.z_score(filled, mean, var)
+        got = out[k + "_z"].values.cpu().numpy()
+        assert helpers.zscore_close(got, want, mean, var), k
+    assert state.mean_var_of("const") == (7.5, 0.0)
+    assert np.array_equal(out["const_z"].values.cpu().numpy(), np.zeros(n, np.float32))
+
+
+def test_empty_table(ktw, fn):
+    from kubeflow_tfx_workshop_b200 import synth
+    host = synth.taxi_table(0, backend="numpy")
+    eng = ktw.Engine(ktw.trace(fn, synth.TAXI_SCHEMA))
+    out, state = eng.analyze_and_transform(host.to("cuda"))
+    assert len(out) == 0
+    assert state.vocabs[("company", 1000, None)].terms() == [O.EMPTY_VOCAB_SENTINEL]
+
+
+def test_errors_are_python_exceptions(ktw):
+    nat = ktw._native
+    with pytest.raises(nat.NativeError, match="ncols"):
+        nat.call("txf_moments_finalize", 1, 0, 1, None)
+    with pytest.raises(nat.NativeError, match="power of two"):
+        nat.call("txf_vocab_compact", 1, 1000, 1, 1, 1, 1, None)
+    with pytest.raises(TypeError):
+        ktw.tft.bucketize(ktw.graph.Const(1.0), 2.5)
+    with pytest.raises(ValueError):
+        ktw.tft.bucketize(ktw.graph.Const(1.0), 0)

@@ -1,0 +1,278 @@
+"""CPU tests of the host side: C-ABI exports, shims/plan tracing, ingest, device-function logic
+compiled for the host, and the multi-rank exchange over gloo."""
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+import helpers
+from helpers import O, ROOT
+
+
+@pytest.fixture(scope="module")
+def ktw():
+    import kubeflow_tfx_workshop_b200 as k
+    return k
+
+
+def test_library_exports_every_declared_symbol(ktw):
+    """libtaxi_xf.so loads and exports exactly what include/taxi_xf.h declares."""
+    header = open(os.path.join(ROOT, "include", "taxi_xf.h")).read()
+    declared = sorted(set(re.findall(r"TXF_API [\w\s\*]*?(txf_\w+)\(", header)))
+    out = subprocess.run(["nm", "-D", "--defined-only", ktw._native.LIB_PATH], capture_output=True, text=True, check=True).stdout
+    exported = sorted(l.split()[-1] for l in out.splitlines() if " T txf_" in l)
+    assert declared == exported == ktw._native.EXPORTED
+    assert ktw._native.query("txf_abi_version") == 1
+    assert ktw._native.query("txf_moments_workspace_bytes", 3) > 0
+    assert ktw._native.query("txf_vocab_table_bytes", 1024) == 32 * 1024
+    assert ktw._native.query("txf_msel_state_bytes", 4, 18) > ktw._native.query("txf_msel_hist_bytes", 4, 18) == 4 * 18 * 256 * 8
+
+
+def test_no_cpu_fallback_without_library(tmp_path):
+    """The product path fails loudly when the CUDA library is missing."""
+    code = ("import sys; sys.path.insert(0, %r)\n"
+            "import importlib.util, os\n"
+            "p = os.path.join(%r, 'kubeflow-tfx-workshop_b200', '_native.py')\n"
+            "src = open(p).read().replace('libtaxi_xf.so', 'libtaxi_xf_missing.so')\n"
+            "ns = {'__file__': p, '__name__': 'native_probe'}\n"
+            "try:\n    exec(compile(src, p, 'exec'), ns)\nexcept ImportError as e:\n    print('IMPORT-ERROR', e)\n" % (ROOT, ROOT))
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True).stdout
+    assert "IMPORT-ERROR" in out and "no CPU fallback" in out
+
+
+def test_product_package_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "kubeflow-tfx-workshop_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                text = open(os.path.join(dirpath, f)).read()
+                assert "tft_oracle" not in text and "liboracle" not in text and "from oracle" not in text, f
+
+
+def test_engine_refuses_cpu_device(ktw):
+    plan = ktw.trace(helpers.load_example_preprocessing_fn(ktw).preprocessing_fn, ktw.synth.TAXI_SCHEMA) if hasattr(ktw, "synth") else None
+    from kubeflow_tfx_workshop_b200 import synth
+    plan = ktw.trace(helpers.load_example_preprocessing_fn(ktw).preprocessing_fn, synth.TAXI_SCHEMA)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        ktw.Engine(plan, device="cpu")
+
+
+def test_trace_example_preprocessing_fn(ktw):
+    from kubeflow_tfx_workshop_b200 import plan as P, synth
+    mod = helpers.load_example_preprocessing_fn(ktw)
+    plan = ktw.trace(mod.preprocessing_fn, synth.TAXI_SCHEMA)
+    kinds = [type(s).__name__ for s in plan.specs]
+    assert kinds == ["ZScoreSpec"] * 3 + ["VocabSpec"] * 2 + ["BucketSpec"] * 4 + ["FillSpec"] * 7 + ["RatioLabelSpec"]
+    v = plan.of(P.VocabSpec)[0]
+    assert (v.top_k, v.num_oov_buckets, v.default_value) == (1000, 10, -1)
+    lab = plan.of(P.RatioLabelSpec)[0]
+    assert (lab.fare_key, lab.tips_key) == ("fare", "tips") and lab.ratio == pytest.approx(0.2)
+    assert plan.output_schema()["pickup_census_tract_xf"] == "bytes" and plan.output_schema()["trip_seconds_xf"] == "float32"
+    assert "trip_start_timestamp" not in plan.input_keys()
+
+
+@pytest.mark.skipif(not os.path.exists("/root/reference/airflow-dags/taxi_utils.py"), reason="reference checkout not present")
+def test_reference_taxi_utils_runs_unmodified_through_the_shims(ktw):
+    """airflow-dags/taxi_utils.py imports tensorflow / tft / tfma and its preprocessing_fn traces
+    to the same plan as examples/taxi_preprocessing.py."""
+    import importlib.util
+    from kubeflow_tfx_workshop_b200 import synth
+    with ktw.install_shims():
+        spec = importlib.util.spec_from_file_location("ref_taxi_utils", "/root/reference/airflow-dags/taxi_utils.py")
+        ref = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(ref)
+    assert "tensorflow" not in sys.modules or sys.modules["tensorflow"].__name__ != "kubeflow_tfx_workshop_b200.tf_shim"
+    schema = dict(synth.TAXI_SCHEMA, trip_start_timestamp="int64")
+    a = ktw.trace(ref.preprocessing_fn, schema)
+    b = ktw.trace(helpers.load_example_preprocessing_fn(ktw).preprocessing_fn, schema)
+    assert a.specs == b.specs
+    assert ref._transformed_name("fare") == "fare_xf"
+
+
+def test_notebook_06_variant_with_sparse_to_dense(ktw):
+    """notebooks/06_Airflow_Feature_Analysis.ipynb:176 uses tf.sparse_to_dense(indices, shape, values, default)."""
+    tf, tft = ktw.tf, ktw.tft
+
+    def fill(x):
+        default_value = '' if x.dtype == tf.string else 0
+        return tf.squeeze(tf.sparse_to_dense(x.indices, [x.dense_shape[0], 1], x.values, default_value), axis=1)
+
+    plan = ktw.trace(lambda inputs: {"a": tft.scale_to_z_score(fill(inputs["x"])), "b": fill(inputs["s"])}, {"x": "float32", "s": "bytes"})
+    assert [type(s).__name__ for s in plan.specs] == ["ZScoreSpec", "FillSpec"]
+
+
+def test_unsupported_expressions_raise(ktw):
+    tf, tft = ktw.tf, ktw.tft
+    with pytest.raises(NotImplementedError):
+        ktw.trace(lambda i: {"a": tf.multiply(tf.squeeze(tf.sparse.to_dense(i["x"], 0), axis=1), 2.0)}, {"x": "float32"})
+    with pytest.raises(NotImplementedError):  # fill value other than '' / 0
+        ktw.trace(lambda i: {"a": tf.squeeze(tf.sparse.to_dense(i["x"], 7), axis=1)}, {"x": "float32"})
+    with pytest.raises(TypeError):
+        tft.bucketize(ktw.graph.Const(1.0), "10")
+    with pytest.raises(ValueError):
+        tft.bucketize(ktw.graph.Const(1.0), 0)
+    with pytest.raises(ValueError):
+        tft.compute_and_apply_vocabulary(ktw.graph.Const("a"), top_k=0)
+    with pytest.raises(TypeError):
+        tft.scale_to_z_score(ktw.graph.Const("a"))
+
+
+def test_table_ingest_rows_arrow_csv(ktw, tmp_path):
+    rows = [{"f": [1.5], "i": [3], "s": [b"ab"]}, {"f": [], "i": None, "s": []}, {"f": 2.5, "i": [4], "s": "cd"}]
+    t = ktw.Table.from_rows(rows, {"f": "float32", "i": "int64", "s": "bytes"})
+    assert t["f"].values.tolist() == [1.5, 0.0, 2.5] and t["f"].numpy()[1].tolist() == [True, False, True]
+    assert t["s"].to_list() == [b"ab", b"", b"cd"] and t["s"].numpy()[2].tolist() == [True, False, True]
+    with pytest.raises(ValueError, match="at most one value"):
+        ktw.Table.from_rows([{"f": [1.0, 2.0]}], {"f": "float32"})
+    import pyarrow as pa
+    at = pa.table({"f": pa.array([1.0, None, 3.0]), "i": pa.array([1, 2, None]), "s": pa.array(["x", None, "yz"]), "z": pa.nulls(3)})
+    t2 = ktw.Table.from_arrow(at)
+    assert t2["f"].dtype == "float32" and t2["i"].dtype == "int64" and t2["s"].to_list() == [b"x", b"", b"yz"] and t2["z"].dtype == "bytes"
+    assert t2["s"].pool.numel() >= t2["s"].pool_bytes + 16
+    p = tmp_path / "d.csv"
+    p.write_text("a,b,c,d\n1,2.5,x,\n,3,y,\n7,,,\n")
+    t3 = ktw.Table.from_csv(str(p))
+    assert t3.schema() == {"a": "int64", "b": "float32", "c": "bytes", "d": "bytes"}
+    assert t3["a"].values.tolist() == [1, 0, 7] and t3["c"].to_list() == [b"x", b"y", b""]
+
+
+@pytest.mark.skipif(not os.path.exists("/root/reference/airflow-dags/data/taxi_data/data.csv"), reason="reference checkout not present")
+def test_csv_ingest_of_bundled_data_matches_fixture(ktw):
+    t = ktw.Table.from_csv("/root/reference/airflow-dags/data/taxi_data/data.csv")
+    cols, _, _ = helpers.load_taxi_golden()
+    for k, c in cols.items():
+        got = t[k]
+        if isinstance(c, O.StrCol):
+            assert got.to_list() == c.to_list(), k
+        else:
+            v, valid = got.numpy()
+            assert v.dtype == c.values.dtype and np.array_equal(valid, c.valid), k
+            assert np.array_equal(np.where(valid, v, 0), np.where(c.valid, c.values, 0)), k
+
+
+def test_device_hash_and_key_logic_compiled_for_host(tmp_path):
+    """farmhash.cuh / common.cuh helpers are __host__ __device__: compile them with g++ through nvcc
+    and check them against the oracle without a GPU."""
+    src = tmp_path / "hostcheck.cu"
+    src.write_text(r'''
+#include <cstdio>
+#include <cstring>
+#include <vector>
+#include "common.cuh"
+#include "farmhash.cuh"
+namespace txf { void set_error(const char*, ...) {} int check_cuda(cudaError_t, const char*) { return 0; } void count_launch(int) {} }
+int main(int argc, char** argv) {
+  FILE* f = fopen(argv[1], "rb");
+  std::vector<unsigned char> buf(1 << 22, 0);
+  size_t n = fread(buf.data() + 8, 1, buf.size() - 64, f);
+  fclose(f);
+  size_t pos = 8;
+  while (pos < 8 + n) {
+    unsigned len; memcpy(&len, &buf[pos], 4); pos += 4;
+    uint64_t fp, tag; txf::fingerprint128(&buf[pos], len, fp, tag);
+    printf("%llu\n", (unsigned long long)fp);
+    pos += len;
+  }
+  float probes[] = {-1.5f, -0.0f, 0.0f, 1e-45f, 2.0f};
+  for (float p : probes) printf("K %u %08x\n", txf::f32_key(p), txf::f32_bits(txf::key_f32(txf::f32_key(p))));
+  return 0;
+}
+''')
+    exe = tmp_path / "hostcheck"
+    csrc = os.path.join(ROOT, "kubeflow-tfx-workshop_b200", "csrc")
+    subprocess.run(["nvcc", "-O1", "-std=c++17", "-I", csrc, "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
+    rng = np.random.default_rng(5)
+    items = [bytes(rng.integers(0, 256, L, dtype=np.uint8)) for L in list(range(0, 130)) + [200, 511, 512, 513]]
+    blob = b"".join(len(s).to_bytes(4, "little") + s for s in items)
+    (tmp_path / "in.bin").write_bytes(blob)
+    out = subprocess.run([str(exe), str(tmp_path / "in.bin")], capture_output=True, text=True, check=True).stdout.split("\n")
+    got = [int(x) for x in out[: len(items)]]
+    assert got == [O.fingerprint64_c(s) for s in items]
+    keys = [l.split() for l in out if l.startswith("K ")]
+    probes = np.array([-1.5, -0.0, 0.0, 1e-45, 2.0], np.float32)
+    assert [int(k[1]) for k in keys] == O.order_key(probes).tolist()
+    assert [int(k[2], 16) for k in keys] == O.key_to_f32(O.order_key(probes)).view(np.uint32).tolist()
+
+
+def test_shard_range(ktw):
+    n = 1_000_003
+    spans = [ktw.shard_range(n, r, 8) for r in range(8)]
+    assert spans[0][0] == 0 and spans[-1][1] == n
+    assert all(a[1] == b[0] for a, b in zip(spans, spans[1:])) and all(lo % 8 == 0 for lo, _ in spans)
+    assert ktw.shard_range(5, 3, 4) == (5, 5)
+
+
+def _gloo_worker(rank, world, port, q):
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import kubeflow_tfx_workshop_b200 as ktw
+        from kubeflow_tfx_workshop_b200 import synth
+        comm = ktw.Comm()
+        n = 20_001
+        lo, hi = ktw.shard_range(n, rank, world)
+        cols = helpers.oracle_from_table(synth.taxi_table(hi - lo, lo, backend="numpy"))
+        part = O.analyze_partial(cols)
+        # Welford triples: all-gather, merge in rank order (what txf_moments_merge does on the GPU)
+        mine = torch.tensor([part["moments"][k] for k in O.DENSE_FLOAT_KEYS], dtype=torch.float64)
+        allm = comm.all_gather(mine)
+        merged = {}
+        for j, k in enumerate(O.DENSE_FLOAT_KEYS):
+            acc = (0.0, 0.0, 0.0)
+            for r in range(world):
+                acc = O.merge_moments(acc, tuple(allm[r, j].tolist()))
+            merged[k] = acc
+        # integer histograms of the quantile keys: all-reduce(sum)
+        hist = torch.stack([torch.from_numpy(np.bincount(part["qkeys"][k] >> 16, minlength=1 << 16)) for k in O.BUCKET_KEYS])
+        comm.all_reduce_sum_(hist)
+        # variable-length exchange (candidate keys / vocabulary entries): rank-ordered concatenation
+        keys0 = torch.from_numpy(part["qkeys"][O.BUCKET_KEYS[0]].astype(np.int64))
+        allk, counts = comm.all_gather_var(torch.cat([keys0, torch.zeros(5, dtype=torch.int64)]), keys0.numel())
+        terms = sorted(part["vocab"]["company"].items())
+        pool = torch.from_numpy(np.frombuffer(b"".join(t for t, _ in terms) or b"\0", np.uint8).copy())
+        lens = torch.tensor([len(t) for t, _ in terms], dtype=torch.int64)
+        cnts = torch.tensor([c for _, c in terms], dtype=torch.int64)
+        g_pool, _ = comm.all_gather_var(pool, int(lens.sum()))
+        g_lens, _ = comm.all_gather_var(lens, len(terms))
+        g_cnts, _ = comm.all_gather_var(cnts, len(terms))
+        buf = g_pool.numpy().tobytes()
+        ends = np.cumsum(g_lens.numpy())
+        vocab = {}
+        for e, L, c in zip(ends, g_lens.numpy(), g_cnts.numpy()):
+            t = buf[e - L:e]
+            vocab[t] = vocab.get(t, 0) + int(c)
+        q.put((rank, merged, hist.sum(dim=1).tolist(), int(allk.numel()), counts, vocab))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_exchange_over_gloo(ktw):
+    """world_size 2, gloo: the collectives used between analyze and transform reproduce the
+    single-process analyzer state."""
+    import torch.multiprocessing as mp
+    from kubeflow_tfx_workshop_b200 import synth
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29500 + os.getpid() % 2000
+    procs = [ctx.Process(target=_gloo_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    results = sorted([q.get(timeout=180) for _ in procs], key=lambda r: r[0])
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    n = 20_001
+    whole = O.analyze_partial(helpers.oracle_from_table(synth.taxi_table(n, backend="numpy")))
+    for rank, merged, hist_tot, nk, counts, vocab in results:
+        for k in O.DENSE_FLOAT_KEYS:
+            assert merged[k][0] == n
+            assert merged[k][1] == pytest.approx(whole["moments"][k][1], rel=1e-12)
+            assert merged[k][2] == pytest.approx(whole["moments"][k][2], rel=1e-10)
+        assert hist_tot == [n] * 4 and nk == n and sum(counts) == n
+        assert vocab == dict(whole["vocab"]["company"])
+    assert results[0][1] == results[1][1]  # identical on every rank (rank-ordered merge)
