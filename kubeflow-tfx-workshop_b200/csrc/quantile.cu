@@ -379,7 +379,7 @@ static int fill_view(NumColsView& v, const void* const* values, const uint8_t* c
   TXF_REQUIRE(ncols >= 1 && ncols <= TXF_MAX_COLS, "%s: ncols=%d out of [1,%d]", who, ncols, TXF_MAX_COLS);
   TXF_REQUIRE(values != nullptr, "%s: null column table", who);
   for (int c = 0; c < ncols; ++c) {
-    TXF_REQUIRE(values[c] != nullptr && aligned(values[c], 16), "%s: column %d values null or not 16B aligned", who, c);
+    TXF_REQUIRE(values[c] != nullptr && aligned(values[c], raw ? 4 : 16), "%s: column %d values null or misaligned", who, c);
     v.values[c] = values[c];
     v.valid[c] = (valid && !raw) ? valid[c] : nullptr;
     v.dtype[c] = (dtype && !raw) ? dtype[c] : TXF_F32;

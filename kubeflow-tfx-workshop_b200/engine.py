@@ -297,7 +297,9 @@ class Engine:
         edges = self._msel(f"q{nb}_edges", ncols, 2 * T, er, sample_pass, reduce=False)
         # (3) the one streaming pass over the column
         cells = self._buf(f"q{nb}_cells", (ncols, 4 * T + 1), torch.int64, zero=True)
-        cand_cap = max(1 << 16, n_local // 8)
+        # keys strictly inside a bracket are kept: expect (bracket width / sample size) of the rows
+        frac = sum(hi - lo + 2 for lo, hi in zip(edges_ranks[0::2], edges_ranks[1::2])) / max(M_sum, 1)
+        cand_cap = max(1 << 16, min(int(1.5 * frac * n_local) + 4096, max(n_local, 1)))
         cand = self._buf(f"q{nb}_cand", (ncols, cand_cap), torch.int32)
         cand_count = self._buf(f"q{nb}_cand_count", (ncols,), torch.int64, zero=True)
         for ch in chunks:
