@@ -33,7 +33,7 @@ extern "C" {
 #define TXF_ABI_VERSION 1
 #define TXF_MAX_COLS 16   /* columns handled by one analyzer launch */
 #define TXF_MAX_OPS 32    /* column ops in one fused transform program */
-#define TXF_POOL_SLACK 16 /* readable bytes required past the end of a string pool */
+#define TXF_POOL_SLACK 32 /* readable bytes required past the end of a string pool */
 #define TXF_QMAX_TARGETS 64 /* bracket-count fast path: at most this many boundaries */
 
 enum { TXF_OK = 0, TXF_ERR_ARG = -1, TXF_ERR_CUDA = -2, TXF_ERR_CAPACITY = -3 };
@@ -116,18 +116,30 @@ TXF_API int txf_qfinal(const uint32_t* direct_key_dev, const uint64_t* cand_rank
 
 /* ------------------------------------------------------------------------------------------
  * Vocabulary analyzer -- tft.compute_and_apply_vocabulary(top_k, num_oov_buckets)
- * (taxi_utils.py:121-126): exact occurrence counts in an open-addressing table keyed by
- * (Fingerprint64, tag), first-seen bytes kept in an arena, then the top_k terms by
- * (count, bytes) descending.
+ * (taxi_utils.py:121-126): exact occurrence counts in an open-addressing table keyed by the
+ * term identity, first-seen bytes kept in an arena, then the top_k terms by (count, bytes)
+ * descending.  Fingerprint64 is evaluated only for out-of-vocabulary terms.
  *
- * table: capacity (power of two) slots of 32 bytes {u64 fp, u64 tag, u64 count, u64 strref};
+ * table: capacity (power of two) slots of 32 bytes {u64 a, u64 b, u64 count, u64 strref}, (a, b) being
+ * the term's 128-bit identity (the bytes themselves up to 15 bytes, a double hash beyond);
  * ctrl_dev: u64[8] = {arena_used, slots_used, overflow, kept, total, sel, 0, 0}.
  * Both must be zero-initialised by the caller before the first count.
  * ------------------------------------------------------------------------------------------ */
 TXF_API size_t txf_vocab_table_bytes(int64_t capacity);
+/* codes_dev (optional, uint32[n]) receives the dictionary code of every row's term and
+ * local2global_dev (uint32[txf_vocab_local_codes()]) the table slot behind each CTA-local code;
+ * txf_vocab_final_codes turns them into a decode table the fused transform gathers from, so
+ * analyze+transform of the SAME rows never re-reads or re-hashes the term bytes. */
+TXF_API int64_t txf_vocab_local_codes(void);
 TXF_API int txf_vocab_count(const int32_t* offsets_dev, const uint8_t* pool_dev, const uint8_t* valid_dev, int64_t n,
                     void* table_dev, int64_t capacity, uint8_t* arena_dev, int64_t arena_cap,
-                    uint64_t* ctrl_dev, txf_stream_t stream);
+                    uint64_t* ctrl_dev, uint32_t* codes_dev, uint32_t* local2global_dev, txf_stream_t stream);
+/* final_code_dev: int64[txf_vocab_local_codes() + capacity]; lookup_dev: the vocabulary's lookup
+ * table (txf_vocab_build_lookup); semantics of the value = TXF_OP_VOCAB's output for that term */
+TXF_API int txf_vocab_final_codes(const void* table_dev, int64_t capacity, const uint8_t* arena_dev,
+                          const uint32_t* local2global_dev, const void* lookup_dev, int64_t lookup_cap,
+                          int64_t vocab_size, int64_t num_oov_buckets, int64_t default_value,
+                          int64_t* final_code_dev, txf_stream_t stream);
 /* dense list of occupied slots: ent_dev[capacity] (u32 slot ids), ctrl[4] = total distinct.
  * Terms tft never admits ('' and anything containing \n or \r) are listed last and not
  * counted in ctrl[3] = kept; counts_dev[i] = count of ent_dev[i] saturated to u32. */
@@ -173,7 +185,9 @@ enum {
   TXF_OP_FILL_I64 = 3,   /* :132-133  out i64 = fill(x) */
   TXF_OP_FILL_F32 = 4,   /* :132-133  out f32 = fill(x) */
   TXF_OP_FILL_STR = 5,   /* :132-133  out int32 offsets rebased to 0 (bytes are copied by the caller) */
-  TXF_OP_RATIO_LABEL = 6 /* :135-143  out i64 = isnan(in0) ? 0 : (in1 > in0 * f0); in0 = fare, in1 = tips */
+  TXF_OP_RATIO_LABEL = 6, /* :135-143  out i64 = isnan(in0) ? 0 : (in1 > in0 * f0); in0 = fare, in1 = tips */
+  TXF_OP_VOCAB_CODED = 7  /* :121-126  in0 = uint32 codes from txf_vocab_count, p0 = int64 decode table
+                                       (txf_vocab_final_codes); out i64 = table[code] */
 };
 
 typedef struct txf_op {

@@ -14,10 +14,10 @@ LIB_PATH = os.path.join(_HERE, "libtaxi_xf.so")
 
 TXF_MAX_COLS = 16
 TXF_MAX_OPS = 32
-TXF_POOL_SLACK = 16
+TXF_POOL_SLACK = 32
 TXF_QMAX_TARGETS = 64
 TXF_F32, TXF_I64 = 0, 1
-(OP_ZSCORE, OP_VOCAB, OP_BUCKETIZE, OP_FILL_I64, OP_FILL_F32, OP_FILL_STR, OP_RATIO_LABEL) = range(7)
+(OP_ZSCORE, OP_VOCAB, OP_BUCKETIZE, OP_FILL_I64, OP_FILL_F32, OP_FILL_STR, OP_RATIO_LABEL, OP_VOCAB_CODED) = range(8)
 
 
 class NativeError(RuntimeError):
@@ -65,7 +65,9 @@ _SIGNATURES = {
     "txf_vocab_table_bytes": (c_size_t, [c_int64]),
     "txf_vocab_lookup_bytes": (c_size_t, [c_int64]),
     "txf_vocab_sort_scratch_bytes": (c_size_t, [c_int64]),
-    "txf_vocab_count": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p]),
+    "txf_vocab_local_codes": (c_int64, []),
+    "txf_vocab_count": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "txf_vocab_final_codes": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_void_p, c_void_p]),
     "txf_vocab_compact": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "txf_vocab_export_meta": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "txf_vocab_export_bytes": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p]),

@@ -31,9 +31,7 @@ __global__ void fingerprint_kernel(const int32_t* __restrict__ offsets, const ui
   int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
   if (i >= n) return;
   int32_t b = offsets[i], e = offsets[i + 1];
-  uint64_t fp, tag;
-  fingerprint128(pool + b, static_cast<uint32_t>(e - b), fp, tag);
-  out[i] = fp;
+  out[i] = fingerprint64(pool + b, static_cast<uint32_t>(e - b));
 }
 
 }  // namespace txf

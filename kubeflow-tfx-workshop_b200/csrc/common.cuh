@@ -40,12 +40,12 @@ struct NumColsView {
 // ---- validity -------------------------------------------------------------------------------
 // Arrow bitmap, LSB first; nullptr == every row present.
 __device__ __forceinline__ bool row_valid(const uint8_t* valid, int64_t i) {
-  return valid == nullptr || ((valid[i >> 3] >> (i & 7)) & 1);
+  return valid == nullptr || ((__ldg(valid + (i >> 3)) >> (i & 7)) & 1);
 }
 // 4 validity bits of the quad starting at row q4 (q4 % 4 == 0)
 __device__ __forceinline__ uint32_t quad_valid(const uint8_t* valid, int64_t q4) {
   if (valid == nullptr) return 0xFu;
-  return (static_cast<uint32_t>(valid[q4 >> 3]) >> (q4 & 4)) & 0xFu;
+  return (static_cast<uint32_t>(__ldg(valid + (q4 >> 3))) >> (q4 & 4)) & 0xFu;
 }
 
 // ---- canonical order-preserving key of an fp32 (NaN last, -0 == +0) -----------------------

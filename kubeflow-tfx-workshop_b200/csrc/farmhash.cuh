@@ -1,11 +1,9 @@
-// farmhash.cuh -- device FarmHash Fingerprint64 (farmhashna::Hash64) plus a second 64-bit tag.
+// farmhash.cuh -- device FarmHash Fingerprint64 (farmhashna::Hash64).
 //
 // Replaces TF's StringToHashBucketFast on the OOV branch of
-// tft.compute_and_apply_vocabulary (reference call site airflow-dags/taxi_utils.py:123-126)
-// and doubles as the key of the vocabulary count/lookup tables.  Written from the published
-// algorithm; `tag` is NOT part of FarmHash: it is an independent mix
-// of the two words FarmHash feeds to its final HashLen16, so (fp, tag) is a 128-bit identity
-// of the string at the cost of two extra multiplies.
+// tft.compute_and_apply_vocabulary (reference call site airflow-dags/taxi_utils.py:123-126).
+// Written from the published algorithm.  It is only evaluated for terms
+// that are NOT in the vocabulary; table identities use the cheaper key of vocab.cuh.
 //
 // All fetches are unaligned little-endian 8-byte reads assembled from two ALIGNED 8-byte
 // loads, so the byte buffer must be readable up to the next 8-byte boundary past the last
@@ -18,8 +16,6 @@ namespace txf {
 constexpr uint64_t kK0 = 0xc3a5c85c97cb3127ULL;
 constexpr uint64_t kK1 = 0xb492b66fbe98f273ULL;
 constexpr uint64_t kK2 = 0x9ae16a3b2f90404fULL;
-constexpr uint64_t kQ1 = 0x9e3779b97f4a7c15ULL;  // tag mixers (not FarmHash constants)
-constexpr uint64_t kQ2 = 0xd6e8feb86659fd93ULL;
 
 __host__ __device__ __forceinline__ uint64_t fetch64(const uint8_t* p) {
   uintptr_t a = reinterpret_cast<uintptr_t>(p);
@@ -38,10 +34,6 @@ __host__ __device__ __forceinline__ uint64_t hash_len16(uint64_t u, uint64_t v, 
   b ^= b >> 47;
   return b * m;
 }
-__host__ __device__ __forceinline__ uint64_t make_tag(uint64_t u, uint64_t v, uint64_t m) {
-  uint64_t t = (u * kQ1) ^ rotr64(v * kQ2, 31) ^ m;
-  return t ^ (t >> 29);
-}
 __host__ __device__ __forceinline__ void weak_hash32(const uint8_t* p, uint64_t a, uint64_t b, uint64_t& o0,
                                                      uint64_t& o1) {
   uint64_t w = fetch64(p), x = fetch64(p + 8), y = fetch64(p + 16), z = fetch64(p + 24);
@@ -55,8 +47,8 @@ __host__ __device__ __forceinline__ void weak_hash32(const uint8_t* p, uint64_t 
   o1 = b + c;
 }
 
-// Fingerprint64 of s[0..n) and the side tag.
-__host__ __device__ inline void fingerprint128(const uint8_t* s, uint32_t n, uint64_t& fp, uint64_t& tag) {
+// Fingerprint64 of s[0..n).
+__host__ __device__ inline uint64_t fingerprint64(const uint8_t* s, uint32_t n) {
   uint64_t u, v, m;
   if (n <= 16) {
     if (n >= 8) {
@@ -74,13 +66,9 @@ __host__ __device__ inline void fingerprint128(const uint8_t* s, uint32_t n, uin
       uint32_t a = s[0], b = s[n >> 1], c = s[n - 1];
       uint32_t y = a + (b << 8);
       uint32_t z = n + (c << 2);
-      fp = shift_mix(static_cast<uint64_t>(y) * kK2 ^ static_cast<uint64_t>(z) * kK0) * kK2;
-      tag = make_tag(y, z, 3);
-      return;
+      return shift_mix(static_cast<uint64_t>(y) * kK2 ^ static_cast<uint64_t>(z) * kK0) * kK2;
     } else {
-      fp = kK2;
-      tag = make_tag(0, 0, 0);
-      return;
+      return kK2;
     }
   } else if (n <= 32) {
     m = kK2 + static_cast<uint64_t>(n) * 2;
@@ -137,8 +125,7 @@ __host__ __device__ inline void fingerprint128(const uint8_t* s, uint32_t n, uin
     u = hash_len16(v0, w0, m) + shift_mix(y) * kK0 + z;
     v = hash_len16(v1, w1, m) + x;
   }
-  fp = hash_len16(u, v, m);
-  tag = make_tag(u, v, m);
+  return hash_len16(u, v, m);
 }
 
 }  // namespace txf

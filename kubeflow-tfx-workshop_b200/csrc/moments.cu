@@ -107,17 +107,29 @@ __global__ void __launch_bounds__(kMomBlock) moments_partial_kernel(NumColsView 
   }
 }
 
-// one thread per column folds the block partials (fixed order) and then the running state
+// one warp per column folds the block partials: lane l takes partials l, l+32, ... in order, then
+// the lanes merge in a fixed butterfly -- a fixed tree, so the result is reproducible -- and the
+// running state is merged last
 __global__ void moments_fold_kernel(const double* __restrict__ partials, int nblocks, int ncols,
                                     double* __restrict__ state) {
-  int c = threadIdx.x;
+  const int c = blockIdx.x;
   if (c >= ncols) return;
-  Triple r{0.0, 0.0, 0.0};
+  Triple t{0.0, 0.0, 0.0};
   const double* p = partials + static_cast<int64_t>(c) * nblocks * 3;
-  for (int b = 0; b < nblocks; ++b) r = chan(r, Triple{p[3 * b], p[3 * b + 1], p[3 * b + 2]});
-  Triple s{state[3 * c], state[3 * c + 1], state[3 * c + 2]};
-  s = chan(s, r);
-  state[3 * c] = s.n; state[3 * c + 1] = s.mean; state[3 * c + 2] = s.m2;
+  for (int b = lane_id(); b < nblocks; b += 32) t = chan(t, Triple{p[3 * b], p[3 * b + 1], p[3 * b + 2]});
+#pragma unroll
+  for (int off = 1; off < 32; off <<= 1) {
+    Triple o;
+    o.n = __shfl_xor_sync(0xffffffffu, t.n, off);
+    o.mean = __shfl_xor_sync(0xffffffffu, t.mean, off);
+    o.m2 = __shfl_xor_sync(0xffffffffu, t.m2, off);
+    t = (lane_id() & off) ? chan(o, t) : chan(t, o);
+  }
+  if (lane_id() == 0) {
+    Triple s{state[3 * c], state[3 * c + 1], state[3 * c + 2]};
+    s = chan(s, t);
+    state[3 * c] = s.n; state[3 * c + 1] = s.mean; state[3 * c + 2] = s.m2;
+  }
 }
 
 __global__ void moments_merge_kernel(const double* __restrict__ states, int nstates, int ncols,
@@ -175,7 +187,7 @@ int txf_moments_update(const void* const* values, const uint8_t* const* valid, c
   int gx = moments_grid(n, ncols);
   moments_partial_kernel<<<dim3(gx, ncols), kMomBlock, 0, s>>>(v, n, static_cast<double*>(workspace_dev));
   TXF_LAUNCH_CHECK();
-  moments_fold_kernel<<<1, 32, 0, s>>>(static_cast<const double*>(workspace_dev), gx, ncols, state_dev);
+  moments_fold_kernel<<<ncols, 32, 0, s>>>(static_cast<const double*>(workspace_dev), gx, ncols, state_dev);
   TXF_LAUNCH_CHECK();
   count_launch(2);
   return TXF_OK;

@@ -182,20 +182,37 @@ __global__ void msel_resolve_kernel(uint8_t* state, int ncols, int R, int pass) 
   int32_t* slot = reinterpret_cast<int32_t*>(state + L.slot) + static_cast<size_t>(c) * R;
   int32_t* ucount = reinterpret_cast<int32_t*>(state + L.ucount);
   const int U = ucount[c];
-  for (int i = threadIdx.x; i < R; i += blockDim.x) {
-    int s = slot[i];
-    if (s < 0) continue;
-    const unsigned long long* h = hist + static_cast<size_t>(s) * 256;
-    uint64_t r = rem[i], cum = 0;
-    int d = 255;
-    for (int b = 0; b < 256; ++b) {
-      uint64_t hb = h[b];
-      if (r <= cum + hb) { d = b; break; }
-      cum += hb;
+  // one warp per rank: lane l owns bins 8l..8l+7; a warp scan finds the bin holding the rank
+  const int warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  for (int i = warp; i < R; i += nwarps) {
+    const int s = slot[i];
+    if (s < 0) continue;  // warp-uniform
+    const unsigned long long* h = hist + static_cast<size_t>(s) * 256 + 8 * lane_id();
+    unsigned long long v[8], mine = 0;
+#pragma unroll
+    for (int b = 0; b < 8; ++b) { v[b] = h[b]; mine += v[b]; }
+    unsigned long long incl = mine;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      unsigned long long o = __shfl_up_sync(0xffffffffu, incl, off);
+      if (static_cast<int>(lane_id()) >= off) incl += o;
     }
-    if (d == 255 && r > cum + h[255]) cum = 0;  // rank beyond the data: keep going, result is meaningless
-    prefix[i] = (prefix[i] << 8) | static_cast<uint32_t>(d);
-    rem[i] = r - cum;
+    const unsigned long long r = rem[i];
+    const unsigned long long excl = incl - mine;
+    const unsigned ok = __ballot_sync(0xffffffffu, r <= incl);  // first lane whose prefix reaches the rank
+    const int owner = ok ? __ffs(ok) - 1 : 31;                  // rank beyond the data: last bin, result meaningless
+    if (static_cast<int>(lane_id()) == owner) {
+      unsigned long long cum = excl;
+      int d = 7;
+#pragma unroll
+      for (int b = 0; b < 8; ++b) {
+        if (r <= cum + v[b]) { d = b; break; }
+        cum += v[b];
+      }
+      if (!ok) cum = 0;
+      prefix[i] = (prefix[i] << 8) | static_cast<uint32_t>(8 * owner + d);
+      rem[i] = r - cum;
+    }
   }
   __syncthreads();
   if (threadIdx.x == 0) {  // rebuild the distinct-prefix table; ranks ascend, so prefixes ascend
@@ -248,48 +265,125 @@ __global__ void qsample_kernel(NumColsView cols, int64_t n, int64_t M, uint64_t 
 }
 
 constexpr int kQBlock = 256;
+constexpr int kQLutBits = 10;            // 1024-entry bin table over [first edge, last edge]
+constexpr int kQTileQuads = 2 * kQBlock; // a tile = 2 quads (8 keys) per thread
+constexpr int kQCandBuf = 4096;          // CTA-local candidate buffer (keys); flushed when half full
 
-// cells: 2p = strictly between edge p-1 and edge p (p = 0..E), 2p+1 = equal to edge p (p < E)
+__device__ __forceinline__ float4 load_quad_as_f32(const void* values, int dtype, int64_t q) {
+  if (dtype == TXF_F32) return ldg_f4(static_cast<const float*>(values) + 4 * q);
+  const long long* v = static_cast<const long long*>(values) + 4 * q;
+  longlong2 a = ldg_l2(v), b = ldg_l2(v + 2);
+  return make_float4(i64_to_f32(a.x), i64_to_f32(a.y), i64_to_f32(b.x), i64_to_f32(b.y));
+}
+
+// cells: 2p = strictly between edge p-1 and edge p (p = 0..E), 2p+1 = equal to edge p (p < E).
+// Locating a key among the edges is a table lookup, not a search: the key range spanned by the
+// edges is cut into 1024 equal bins; each bin stores how many edges lie below it and whether an
+// edge falls inside it (only then are a few edges compared).  Keys strictly inside a bracket are
+// collected in a CTA-local shared-memory buffer and written out in batches, so the streaming
+// loop never waits on a global atomic; the next tile's loads are issued before the current tile
+// is processed.
 __global__ void __launch_bounds__(kQBlock) qcount_kernel(NumColsView cols, int64_t n, int T,
                                                          const uint32_t* __restrict__ edges_all,
                                                          unsigned long long* __restrict__ cells_all,
                                                          uint32_t* __restrict__ cand_all,
                                                          unsigned long long* __restrict__ cand_count, int64_t cand_cap) {
   extern __shared__ uint32_t smem[];
+  __shared__ uint32_t s_ncand;
+  __shared__ unsigned long long s_base;
   const int c = blockIdx.y;
   const int E = 2 * T, ncell = 2 * E + 1;
-  uint32_t* s_edges = smem;                                            // [E]
-  uint16_t* s_cnt = reinterpret_cast<uint16_t*>(smem + ((E + 1) & ~1)); // [ncell][kQBlock], private per thread
+  uint32_t* s_edges = smem;                                                     // [E]
+  uint32_t* s_cand = smem + ((E + 1) & ~1);                                     // [kQCandBuf]
+  uint16_t* s_lut = reinterpret_cast<uint16_t*>(s_cand + kQCandBuf);            // [1 << kQLutBits]
+  uint16_t* s_cnt = s_lut + (1 << kQLutBits);                                   // [ncell][kQBlock], private per thread
   for (int i = threadIdx.x; i < E; i += kQBlock) s_edges[i] = edges_all[static_cast<size_t>(c) * E + i];
   for (int i = threadIdx.x; i < ncell * kQBlock; i += kQBlock) s_cnt[i] = 0;
+  if (threadIdx.x == 0) s_ncand = 0;
+  __syncthreads();
+  const uint32_t first = s_edges[0], last = s_edges[E - 1];
+  const uint32_t span = last - first;
+  const int shift = span >> kQLutBits ? 32 - kQLutBits - __clz(span) : 0;  // (span >> shift) < 1024
+  for (int j = threadIdx.x; j < (1 << kQLutBits); j += kQBlock) {
+    const uint64_t lo_key = static_cast<uint64_t>(first) + (static_cast<uint64_t>(j) << shift);
+    const uint64_t hi_key = lo_key + ((1ULL << shift) - 1);
+    int p = 0;  // edges below the bin
+    while (p < E && s_edges[p] < lo_key) ++p;
+    const bool inside = p < E && s_edges[p] <= hi_key;
+    s_lut[j] = static_cast<uint16_t>(p | (inside ? 0x8000 : 0));
+  }
   __syncthreads();
   uint32_t* cand = cand_all + static_cast<size_t>(c) * cand_cap;
   // private 16-bit counter of (cell, thread): lanes of a warp sit in 32 different banks, warps w
   // and w+4 share the words (low/high half), so the read-modify-write never bank-conflicts
   const int my_slot = (((threadIdx.x >> 5) & 3) * 32 + static_cast<int>(lane_id())) * 2 + (threadIdx.x >> 7);
   auto visit = [&](uint32_t key) {
-    int lo = 0, len = E;  // lo = number of edges < key
-    while (len > 0) {
-      int half = len >> 1;
-      bool lt = s_edges[lo + half] < key;
-      lo = lt ? lo + half + 1 : lo;
-      len = lt ? len - half - 1 : half;
+    int lo;        // number of edges < key
+    bool eq = false;
+    if (key < first) {
+      lo = 0;
+    } else if (key > last) {
+      lo = E;
+    } else {
+      const uint32_t t = s_lut[(key - first) >> shift];
+      lo = t & 0x7FFF;
+      if (t & 0x8000) {
+        while (lo < E && s_edges[lo] < key) ++lo;
+        eq = lo < E && s_edges[lo] == key;
+      }
     }
-    bool eq = lo < E && s_edges[lo] == key;
-    int cell = 2 * lo + (eq ? 1 : 0);
+    const int cell = 2 * lo + (eq ? 1 : 0);
     s_cnt[cell * kQBlock + my_slot] += 1;      // <= 65535 keys per thread per launch (grid sizing)
-    if ((lo & 1) && !eq) {                     // strictly inside bracket (lo-1)/2: keep the key
-      unsigned peers = __activemask();
-      int leader = __ffs(peers) - 1;
-      unsigned long long base = 0;
-      if (static_cast<int>(lane_id()) == leader) base = atomicAdd(&cand_count[c], static_cast<unsigned long long>(__popc(peers)));
-      base = __shfl_sync(peers, base, leader);
-      unsigned long long pos = base + __popc(peers & ((1u << lane_id()) - 1u));
-      if (pos < static_cast<unsigned long long>(cand_cap)) cand[pos] = key;
-    }
+    if ((lo & 1) && !eq) s_cand[atomicAdd(&s_ncand, 1u)] = key;  // strictly inside bracket (lo-1)/2
   };
-  for_each_key(cols.values[c], cols.valid[c], cols.dtype[c], n, visit);
+  auto visit_quad = [&](float4 x, uint32_t m) {
+    visit(f32_key(m & 1 ? x.x : 0.f)); visit(f32_key(m & 2 ? x.y : 0.f));
+    visit(f32_key(m & 4 ? x.z : 0.f)); visit(f32_key(m & 8 ? x.w : 0.f));
+  };
+  auto flush = [&]() {  // all threads; s_ncand is stable on entry
+    if (threadIdx.x == 0) s_base = atomicAdd(&cand_count[c], static_cast<unsigned long long>(s_ncand));
+    __syncthreads();
+    const uint32_t m = s_ncand;
+    for (uint32_t i = threadIdx.x; i < m; i += kQBlock) {
+      unsigned long long pos = s_base + i;
+      if (pos < static_cast<unsigned long long>(cand_cap)) cand[pos] = s_cand[i];
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) s_ncand = 0;
+    __syncthreads();
+  };
+
+  const void* values = cols.values[c];
+  const uint8_t* __restrict__ valid = cols.valid[c];
+  const int dtype = cols.dtype[c];
+  const int64_t nquads = n >> 2;
+  const int64_t ntiles = (nquads + kQTileQuads - 1) / kQTileQuads;
+  int64_t tile = blockIdx.x;
+  float4 xa = make_float4(0, 0, 0, 0), xb = xa;
+  uint32_t ma = 0, mb = 0;
+  auto load_tile = [&](int64_t t) {
+    const int64_t qa = t * kQTileQuads + threadIdx.x, qb = qa + kQBlock;
+    ma = mb = 0x100;  // bit 8 = "no quad here"
+    if (t < ntiles && qa < nquads) { xa = load_quad_as_f32(values, dtype, qa); ma = quad_valid(valid, 4 * qa); }
+    if (t < ntiles && qb < nquads) { xb = load_quad_as_f32(values, dtype, qb); mb = quad_valid(valid, 4 * qb); }
+  };
+  load_tile(tile);
+  for (; tile < ntiles; tile += gridDim.x) {
+    const float4 ca = xa, cb = xb;
+    const uint32_t cma = ma, cmb = mb;
+    load_tile(tile + gridDim.x);  // prefetch
+    if (!(cma & 0x100)) visit_quad(ca, cma);
+    if (!(cmb & 0x100)) visit_quad(cb, cmb);
+    if (__syncthreads_or(s_ncand > kQCandBuf - 8 * kQBlock)) flush();
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {  // rows past the last full quad
+    const int64_t i = (nquads << 2) + threadIdx.x;
+    const bool present = row_valid(valid, i);
+    visit(dtype == TXF_F32 ? cell_key_f32(static_cast<const float*>(values)[i], present)
+                           : cell_key_i64(static_cast<const long long*>(values)[i], present));
+  }
   __syncthreads();
+  flush();
   // fold the private counters: warp w takes cells w, w+8, ...; lanes stride over the 256 threads
   const int warp = threadIdx.x >> 5;
   for (int cell = warp; cell < ncell; cell += kQBlock / 32) {
@@ -485,7 +579,7 @@ int txf_qcount(const void* const* values, const uint8_t* const* valid, const int
   int rc = fill_view(v, values, valid, dtype, ncols, "qcount", false);
   if (rc) return rc;
   const int E = 2 * T, ncell = 2 * E + 1;
-  size_t smem = static_cast<size_t>((E + 1) & ~1) * 4 + static_cast<size_t>(ncell) * kQBlock * 2;
+  size_t smem = static_cast<size_t>((E + 1) & ~1) * 4 + kQCandBuf * 4 + (2u << kQLutBits) + static_cast<size_t>(ncell) * kQBlock * 2;
   if (smem > 48 * 1024)
     TXF_CUDA(cudaFuncSetAttribute(qcount_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
   int per_sm = static_cast<int>((200 * 1024) / (smem + 1024));

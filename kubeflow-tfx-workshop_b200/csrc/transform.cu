@@ -12,12 +12,16 @@
 // Algorithmic bytes per row (taxi schema): read 98.1 + Lp + Lc, write 120; the
 // label re-reads `fare` (4 B/row) because ops run column by column.
 #include "vocab.cuh"
+#include "str_pipe.cuh"
 
 namespace txf {
 
 constexpr int kXfBlock = 1024;
 constexpr int kXfUnroll = 4;                                   // quads in flight per thread and op
 constexpr int64_t kXfTileRows = 4LL * kXfBlock * kXfUnroll;    // 16384 rows per tile
+constexpr int kXfStageBytes = 48 * 1024;                       // per buffer: staged term bytes of one vocabulary tile
+constexpr int kXfPipeBytes = StrTilePipe::header_bytes() + 2 * kXfStageBytes;
+constexpr int kXfVocabTileRows = 2 * kXfBlock;
 constexpr int kXfSmemBudget = 200 * 1024;
 
 struct XfOp {                // device-side op (txf_op + staging offsets)
@@ -38,6 +42,8 @@ struct XfProgram {
   XfOp ops[TXF_MAX_OPS];
   int32_t nops;
   int32_t smem_bytes;
+  int32_t stage_off;  // byte offset of the string staging buffer (only present with vocabulary ops)
+  int32_t pad;
 };
 
 // ---- element math (shared by the vector path and the scalar tail) ---------------------------
@@ -98,20 +104,17 @@ __device__ __forceinline__ uint64_t mod_u64(uint64_t x, uint64_t d) {
 }
 __device__ __forceinline__ long long vocab1(const uint8_t* str, uint32_t len, const LookupSlot* __restrict__ lut,
                                             uint64_t mask, long long vocab_size, long long num_oov, long long dflt) {
-  uint64_t fp, tag;
-  fingerprint128(str, len, fp, tag);
-  unsigned long long kfp, ktag;
-  table_identity(fp, tag, kfp, ktag);
-  const uint32_t tag32 = static_cast<uint32_t>(ktag);
-  uint64_t idx = home_slot(kfp, mask);
+  const StrKey key = make_key(str, len);
+  uint64_t idx = home_slot(key.a, key.b, mask);
   for (uint64_t probe = 0; probe <= mask; ++probe, idx = (idx + 1) & mask) {
-    const uint4 raw = *reinterpret_cast<const uint4*>(lut + idx);
-    const unsigned long long sfp = (static_cast<unsigned long long>(raw.y) << 32) | raw.x;
-    if (sfp == 0) break;
-    if (sfp == kfp && raw.z == tag32) return static_cast<int32_t>(raw.w);
+    const LookupSlot* s = lut + idx;
+    const unsigned long long sb = s->b;
+    if (sb == 0) break;
+    if (sb == key.b && s->a == key.a) return s->id;
   }
   if (num_oov <= 0) return dflt;
-  return vocab_size + static_cast<long long>(mod_u64(fp, static_cast<uint64_t>(num_oov)));
+  // out of vocabulary: TF's StringToHashBucketFast = Fingerprint64(term) mod num_oov_buckets
+  return vocab_size + static_cast<long long>(mod_u64(fingerprint64(str, len), static_cast<uint64_t>(num_oov)));
 }
 
 __device__ __forceinline__ float cell_f32(const XfOp& op, int64_t row) {  // fill + cast of one cell
@@ -152,6 +155,9 @@ __device__ void op_row(const XfOp& op, const uint8_t* smem, int64_t row, int64_t
       static_cast<long long*>(op.out)[row] = label1(fare, tips, op.f0);
       break;
     }
+    case TXF_OP_VOCAB_CODED:
+      static_cast<long long*>(op.out)[row] = static_cast<const long long*>(op.p0)[static_cast<const uint32_t*>(op.in0)[row]];
+      break;
     default: break;  // TXF_OP_VOCAB has no quad path: its row loop covers the tail
   }
 }
@@ -177,6 +183,7 @@ __device__ __forceinline__ float4 fill_f4(float4 r, uint32_t m) {
   return make_float4(m & 1 ? r.x : 0.f, m & 2 ? r.y : 0.f, m & 4 ? r.z : 0.f, m & 8 ? r.w : 0.f);
 }
 
+constexpr int kLinearBuckets = 32;  // up to 32 boundaries: count them for a whole quad, one broadcast LDS each
 struct NumParams {  // per-op constants of the numeric kinds
   ZScale z;
   const float* b;
@@ -184,6 +191,19 @@ struct NumParams {  // per-op constants of the numeric kinds
   float ratio;
   int32_t base;
 };
+// ids of the 4 cells of a quad: id = number of leading boundaries with !(x < b) (NaN -> nb)
+__device__ __forceinline__ void bucket_quad(float4 x, const NumParams& p, long long (&id)[4]) {
+  if (p.nb > kLinearBuckets) {
+    id[0] = bucket1(x.x, p.b, p.nb); id[1] = bucket1(x.y, p.b, p.nb); id[2] = bucket1(x.z, p.b, p.nb); id[3] = bucket1(x.w, p.b, p.nb);
+    return;
+  }
+  int c0 = 0, c1 = 0, c2 = 0, c3 = 0;
+  for (int j = 0; j < p.nb; ++j) {
+    const float bj = p.b[j];
+    c0 += !(x.x < bj) ? 1 : 0; c1 += !(x.y < bj) ? 1 : 0; c2 += !(x.z < bj) ? 1 : 0; c3 += !(x.w < bj) ? 1 : 0;
+  }
+  id[0] = c0; id[1] = c1; id[2] = c2; id[3] = c3;
+}
 __device__ __forceinline__ NumParams make_params(const XfOp& op, const uint8_t* smem) {
   NumParams p{};
   if (op.kind == TXF_OP_ZSCORE) p.z = make_zscale(static_cast<const float*>(op.p0));
@@ -202,7 +222,7 @@ __device__ __forceinline__ void run_in4(const XfOp& op, const uint8_t* smem, int
   const int kind = op.kind;
   const float* __restrict__ v = static_cast<const float*>(op.in0);
   const float* __restrict__ v1 = static_cast<const float*>(op.in1);
-  const uint8_t* __restrict__ valid = kind == TXF_OP_FILL_STR ? nullptr : op.valid0;
+  const uint8_t* __restrict__ valid = (kind == TXF_OP_FILL_STR || kind == TXF_OP_VOCAB_CODED) ? nullptr : op.valid0;
   const uint8_t* __restrict__ valid1 = op.valid1;
   void* out = op.out;
   TXF_FOR_EACH_TILE(nquads) {
@@ -234,9 +254,18 @@ __device__ __forceinline__ void run_in4(const XfOp& op, const uint8_t* smem, int
           break;
         }
         case TXF_OP_BUCKETIZE:
-          store_i64x4(static_cast<long long*>(out), 4 * q, bucket1(x.x, p.b, p.nb), bucket1(x.y, p.b, p.nb), bucket1(x.z, p.b, p.nb),
-                      bucket1(x.w, p.b, p.nb));
+        {
+          long long id[4];
+          bucket_quad(x, p, id);
+          store_i64x4(static_cast<long long*>(out), 4 * q, id[0], id[1], id[2], id[3]);
+        }
           break;
+        case TXF_OP_VOCAB_CODED: {  // dictionary decode: codes written by the count pass -> final ids
+          const long long* __restrict__ tab = static_cast<const long long*>(op.p0);
+          store_i64x4(static_cast<long long*>(out), 4 * q, __ldg(tab + __float_as_uint(raw[u].x)), __ldg(tab + __float_as_uint(raw[u].y)),
+                      __ldg(tab + __float_as_uint(raw[u].z)), __ldg(tab + __float_as_uint(raw[u].w)));
+          break;
+        }
         default: {  // TXF_OP_RATIO_LABEL: second fp32 column (tips)
           const float4 t = fill_f4(ldg_f4(v1 + 4 * q), quad_valid(valid1, 4 * q));
           store_i64x4(static_cast<long long*>(out), 4 * q, label1(x.x, t.x, p.ratio), label1(x.y, t.y, p.ratio), label1(x.z, t.z, p.ratio),
@@ -286,8 +315,11 @@ __device__ __forceinline__ void run_in8(const XfOp& op, const uint8_t* smem, int
                                                                   zscore1(i64_to_f32(c), p.z), zscore1(i64_to_f32(d), p.z)));
             break;
           default:  // TXF_OP_BUCKETIZE
-            store_i64x4(static_cast<long long*>(out), 4 * q, bucket1(i64_to_f32(a), p.b, p.nb), bucket1(i64_to_f32(b), p.b, p.nb),
-                        bucket1(i64_to_f32(c), p.b, p.nb), bucket1(i64_to_f32(d), p.b, p.nb));
+          {
+            long long id[4];
+            bucket_quad(make_float4(i64_to_f32(a), i64_to_f32(b), i64_to_f32(c), i64_to_f32(d)), p, id);
+            store_i64x4(static_cast<long long*>(out), 4 * q, id[0], id[1], id[2], id[3]);
+          }
             break;
         }
       }
@@ -295,8 +327,9 @@ __device__ __forceinline__ void run_in8(const XfOp& op, const uint8_t* smem, int
   }
 }
 
-// one row per lane: coalesced offsets, neighbouring term bytes, coalesced ids
-__device__ __forceinline__ void run_vocab(const XfOp& op, const uint8_t* smem, int64_t n) {
+// Vocabulary op: row tiles of kXfVocabTileRows rows; the tile's term bytes are staged in shared
+// memory (coalesced 16-byte loads), then one row per lane: coalesced offsets in, coalesced ids out.
+__device__ __forceinline__ void run_vocab(const XfOp& op, const uint8_t* smem, uint8_t* stage, int64_t n) {
   const int32_t* __restrict__ off = static_cast<const int32_t*>(op.in0);
   const uint8_t* __restrict__ valid = op.valid0;
   const uint8_t* __restrict__ pool = op.pool;
@@ -305,12 +338,34 @@ __device__ __forceinline__ void run_vocab(const XfOp& op, const uint8_t* smem, i
   const uint64_t mask = static_cast<uint64_t>(op.a0 - 1);
   const long long vocab_size = op.a1, num_oov = op.a2, dflt = op.a3;
   long long* out = static_cast<long long*>(op.out);
-  const int64_t stride = static_cast<int64_t>(gridDim.x) * kXfBlock;
-  for (int64_t row = static_cast<int64_t>(blockIdx.x) * kXfBlock + threadIdx.x; row < n; row += stride) {
-    int32_t b = __ldg(off + row), e = __ldg(off + row + 1);
-    bool v = row_valid(valid, row);
-    __stcs(out + row, vocab1(pool + b, v ? static_cast<uint32_t>(e - b) : 0u, lut, mask, vocab_size, num_oov, dflt));
+  StrTilePipe pipe;
+  pipe.init(stage, kXfStageBytes, off, pool);
+  const int64_t ntiles = (n + kXfVocabTileRows - 1) / kXfVocabTileRows;
+  auto tile_end = [&](int64_t t) { return (t + 1) * kXfVocabTileRows < n ? (t + 1) * kXfVocabTileRows : n; };
+  if (threadIdx.x == 0) {
+    if (blockIdx.x < ntiles) pipe.issue(blockIdx.x * static_cast<int64_t>(kXfVocabTileRows), tile_end(blockIdx.x), 0);
+    if (blockIdx.x + gridDim.x < ntiles)
+      pipe.issue((blockIdx.x + gridDim.x) * static_cast<int64_t>(kXfVocabTileRows), tile_end(blockIdx.x + gridDim.x), 1);
   }
+  uint32_t k = 0;
+  for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++k) {
+    const int64_t r0 = tile * kXfVocabTileRows;
+    const int64_t r1 = tile_end(tile);
+    const uint8_t* base = pipe.acquire(k & 1, k >> 1);
+#pragma unroll
+    for (int j = 0; j < kXfVocabTileRows / kXfBlock; ++j) {
+      const int64_t row = r0 + j * kXfBlock + threadIdx.x;
+      if (row < r1) {
+        int32_t b = __ldg(off + row), e = __ldg(off + row + 1);
+        bool v = row_valid(valid, row);
+        __stcs(out + row, vocab1(base + b, v ? static_cast<uint32_t>(e - b) : 0u, lut, mask, vocab_size, num_oov, dflt));
+      }
+    }
+    __syncthreads();  // buffer free: refill it with the tile after next
+    const int64_t nxt = tile + 2 * static_cast<int64_t>(gridDim.x);
+    if (threadIdx.x == 0 && nxt < ntiles) pipe.issue(nxt * kXfVocabTileRows, tile_end(nxt), k & 1);
+  }
+  __syncthreads();  // the pipe's shared memory is re-initialised by the next vocabulary op
 }
 
 __global__ void __launch_bounds__(kXfBlock, 1) transform_kernel(const __grid_constant__ XfProgram prog, int64_t n) {
@@ -333,9 +388,9 @@ __global__ void __launch_bounds__(kXfBlock, 1) transform_kernel(const __grid_con
       float* dst = reinterpret_cast<float*>(smem + op.smem_off);
       for (int i = threadIdx.x; i < nb; i += kXfBlock) dst[i] = static_cast<const float*>(op.p0)[i];
     } else if (op.kind == TXF_OP_VOCAB) {
-      uint4* dst = reinterpret_cast<uint4*>(smem + op.smem_off);
-      const uint4* src = static_cast<const uint4*>(op.p0);
-      for (int64_t i = threadIdx.x; i < op.a0; i += kXfBlock) dst[i] = src[i];
+      unsigned long long* dst = reinterpret_cast<unsigned long long*>(smem + op.smem_off);
+      const unsigned long long* src = static_cast<const unsigned long long*>(op.p0);
+      for (int64_t i = threadIdx.x; i < op.a0 * 3; i += kXfBlock) dst[i] = src[i];
     }
   }
   __syncthreads();
@@ -344,7 +399,7 @@ __global__ void __launch_bounds__(kXfBlock, 1) transform_kernel(const __grid_con
   for (int o = 0; o < nops; ++o) {
     const XfOp& op = s_ops[o];
     if (op.kind == TXF_OP_VOCAB)
-      run_vocab(op, smem, n);
+      run_vocab(op, smem, smem + prog.stage_off, n);
     else if (op.kind == TXF_OP_FILL_I64 || ((op.kind == TXF_OP_ZSCORE || op.kind == TXF_OP_BUCKETIZE) && op.in_dtype == TXF_I64))
       run_in8(op, smem, nquads);
     else
@@ -370,7 +425,10 @@ int txf_transform(const txf_op* ops, int nops, int64_t n, txf_stream_t stream) {
   if (n == 0) return TXF_OK;
   XfProgram prog{};
   prog.nops = nops;
-  int smem = 0;
+  bool have_vocab = false;
+  for (int o = 0; o < nops; ++o) have_vocab = have_vocab || ops[o].kind == TXF_OP_VOCAB;
+  int smem = have_vocab ? kXfPipeBytes : 0;  // [string tile pipe][per-op staged state ...]
+  prog.stage_off = 0;
   for (int o = 0; o < nops; ++o) {
     const txf_op& s = ops[o];
     XfOp& d = prog.ops[o];
@@ -394,12 +452,16 @@ int txf_transform(const txf_op* ops, int nops, int64_t n, txf_stream_t stream) {
       case TXF_OP_VOCAB: {
         TXF_REQUIRE(s.p0 != nullptr && s.pool != nullptr, "transform: op %d (vocabulary) needs lookup table and pool", o);
         TXF_REQUIRE(s.a0 >= 2 && (s.a0 & (s.a0 - 1)) == 0, "transform: op %d lookup capacity must be a power of two", o);
-        TXF_REQUIRE(aligned(s.p0, 16), "transform: op %d lookup table not 16B aligned", o);
-        int64_t need = s.a0 * 16;
+        TXF_REQUIRE(aligned(s.p0, 8), "transform: op %d lookup table not 8B aligned", o);
+        have_vocab = true;
+        int64_t need = (s.a0 * static_cast<int64_t>(sizeof(LookupSlot)) + 15) & ~15LL;
         if (smem + need <= kXfSmemBudget) { d.smem_off = smem; smem += static_cast<int>(need); }
         break;
       }
       case TXF_OP_FILL_I64: case TXF_OP_FILL_F32: case TXF_OP_FILL_STR: break;
+      case TXF_OP_VOCAB_CODED:
+        TXF_REQUIRE(s.p0 != nullptr, "transform: op %d (coded vocabulary) needs the decode table p0", o);
+        break;
       case TXF_OP_RATIO_LABEL:
         TXF_REQUIRE(s.in1 != nullptr && aligned(s.in1, 16), "transform: op %d (label) needs in1 (16B aligned)", o);
         TXF_REQUIRE(s.in_dtype == TXF_F32, "transform: op %d (label) takes fp32 columns", o);

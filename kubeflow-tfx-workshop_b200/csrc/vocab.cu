@@ -1,47 +1,56 @@
 // vocab.cu -- vocabulary analyzer of tft.compute_and_apply_vocabulary (reference call site
 // airflow-dags/taxi_utils.py:121-126, top_k=_VOCAB_SIZE :51, num_oov_buckets=_OOV_SIZE :54).
 //
-// Counting: every row's term is identified by (Fingerprint64, tag).  A per-CTA shared-memory
-// table absorbs the hot terms (taxi columns have 7 / ~1000 distinct values) after a warp-level
-// pre-aggregation of equal terms; terms that do not fit go straight to the global
-// open-addressing table (32-byte slots, one DRAM sector per probe).  Counts are exact.  The
+// Counting: one persistent CTA per SM walks row tiles.  The tile's term bytes are staged into
+// shared memory with coalesced 16-byte loads; every row's term gets a 128-bit identity
+// (vocab.cuh: the bytes themselves up to 15 bytes, a double hash beyond) and is counted in a
+// per-CTA shared-memory table (4096 slots) after one warp-level aggregation round; terms that do
+// not fit go straight to the global open-addressing table (32-byte slots, one DRAM sector per
+// probe), into which the front tables are flushed at the end.  Counts are exact.  The
 // first thread to claim a slot copies the term's bytes into an arena, so the table is
 // self-contained: it can be exchanged between ranks and outlives the chunk it was built from.
 // Ranking reproduces tft: drop '' and terms containing \n / \r, order by (count, bytes)
 // descending, keep top_k.
 // Algorithmic bytes of the count pass: 4 (offset) + term bytes per row + 1 validity bit.
 #include "vocab.cuh"
+#include "str_pipe.cuh"
 
 namespace txf {
 
-constexpr int kVcBlock = 256;
-constexpr int kVcSlots = 1024;   // shared-memory front table (24 KB)
+constexpr int kVcBlock = 1024;            // one persistent CTA per SM
+constexpr int kVcSlots = 4096;            // shared-memory front table: 4096 x 24 B = 96 KB
 constexpr int kVcProbes = 8;
-constexpr int kVcAggRounds = 3;  // warp pre-aggregation rounds (covers skewed columns)
+constexpr int kVcRowsPerThread = 2;
+constexpr int kVcTileRows = kVcBlock * kVcRowsPerThread;
+constexpr int kVcStageBytes = 56 * 1024;  // per buffer: staged term bytes of one tile (avg 16 B/row -> 32 KB)
+constexpr size_t kVcSmemBytes = kVcSlots * (8 + 8 + 4 + 4) + StrTilePipe::header_bytes() + 2 * kVcStageBytes;
 constexpr uint32_t kPadEnt = 0xFFFFFFFFu;
+constexpr uint32_t kVcLocalCodes = kSMs * kVcSlots;  // codes below this: (CTA, front-table slot); above: global slot
 
 __device__ __forceinline__ unsigned long long ldcg64(const unsigned long long* p) {
   return __ldcg(p);  // L2 only: never a stale L1 line for words other SMs update atomically
 }
 
-// Add `cnt` occurrences of the term (kfp, ktag) whose bytes are str[0..len) to the global table.
-__device__ void table_add(CountSlot* table, uint64_t mask, unsigned long long kfp, unsigned long long ktag,
-                          unsigned long long cnt, const uint8_t* str, uint32_t len, uint8_t* arena, int64_t arena_cap,
-                          unsigned long long* ctrl) {
-  uint64_t idx = home_slot(kfp, mask);
+// Add `cnt` occurrences of the term with identity (a, b), whose bytes are str[0..len), to the
+// global table; returns the slot index of the term.  Lock-free and exact: a slot is claimed by CAS on word a, then on word b; a term
+// that finds its a but a different b simply moves on to the next slot.
+__device__ uint32_t table_add(CountSlot* table, uint64_t mask, unsigned long long ka, unsigned long long kb,
+                              unsigned long long cnt, const uint8_t* str, uint32_t len, uint8_t* arena, int64_t arena_cap,
+                              unsigned long long* ctrl) {
+  uint64_t idx = home_slot(ka, kb, mask);
   for (uint64_t probe = 0; probe <= mask; ++probe, idx = (idx + 1) & mask) {
     CountSlot* s = table + idx;
-    unsigned long long cur = ldcg64(&s->fp);
+    unsigned long long cur = ldcg64(&s->a);
     if (cur == 0) {
-      cur = atomicCAS(&s->fp, 0ULL, kfp);
-      if (cur == 0) { cur = kfp; atomicAdd(&ctrl[1], 1ULL); }
+      cur = atomicCAS(&s->a, 0ULL, ka);
+      if (cur == 0) { cur = ka; atomicAdd(&ctrl[1], 1ULL); }
     }
-    if (cur != kfp) continue;
-    unsigned long long t = ldcg64(&s->tag);
+    if (cur != ka) continue;
+    unsigned long long t = ldcg64(&s->b);
     if (t == 0) {
-      t = atomicCAS(&s->tag, 0ULL, ktag);
+      t = atomicCAS(&s->b, 0ULL, kb);
       if (t == 0) {  // this thread owns the slot: keep the term's bytes
-        t = ktag;
+        t = kb;
         unsigned long long off = atomicAdd(&ctrl[0], static_cast<unsigned long long>(len));
         if (len > kMaxTermLen || off + len > static_cast<unsigned long long>(arena_cap)) {
           atomicOr(&ctrl[2], 1ULL);
@@ -52,75 +61,93 @@ __device__ void table_add(CountSlot* table, uint64_t mask, unsigned long long kf
         }
       }
     }
-    if (t == ktag) {
+    if (t == kb) {
       atomicAdd(&s->count, cnt);
-      return;
+      return static_cast<uint32_t>(idx);
     }
   }
   atomicOr(&ctrl[2], 2ULL);  // table full
+  return 0xFFFFFFFFu;
 }
 
-__global__ void __launch_bounds__(kVcBlock) vocab_count_kernel(const int32_t* __restrict__ offsets,
-                                                               const uint8_t* __restrict__ pool,
-                                                               const uint8_t* __restrict__ valid, int64_t n,
-                                                               CountSlot* table, uint64_t mask, uint8_t* arena,
-                                                               int64_t arena_cap, unsigned long long* ctrl) {
-  __shared__ unsigned long long s_fp[kVcSlots];
-  __shared__ unsigned long long s_tag[kVcSlots];
-  __shared__ uint32_t s_cnt[kVcSlots];
-  __shared__ uint32_t s_row[kVcSlots];
-  for (int i = threadIdx.x; i < kVcSlots; i += kVcBlock) { s_fp[i] = 0; s_tag[i] = 0; s_cnt[i] = 0; s_row[i] = 0; }
-  __syncthreads();
+__global__ void __launch_bounds__(kVcBlock, 1) vocab_count_kernel(const int32_t* __restrict__ offsets,
+                                                                  const uint8_t* __restrict__ pool,
+                                                                  const uint8_t* __restrict__ valid, int64_t n,
+                                                                  CountSlot* table, uint64_t mask, uint8_t* arena,
+                                                                  int64_t arena_cap, unsigned long long* ctrl,
+                                                                  uint32_t* __restrict__ codes,
+                                                                  uint32_t* __restrict__ local2global) {
+  extern __shared__ __align__(16) uint8_t vc_smem[];
+  unsigned long long* s_a = reinterpret_cast<unsigned long long*>(vc_smem);
+  unsigned long long* s_b = s_a + kVcSlots;
+  uint32_t* s_cnt = reinterpret_cast<uint32_t*>(s_b + kVcSlots);
+  uint32_t* s_row = s_cnt + kVcSlots;
+  for (int i = threadIdx.x; i < kVcSlots; i += kVcBlock) { s_a[i] = 0; s_b[i] = 0; s_cnt[i] = 0; s_row[i] = 0; }
+  StrTilePipe pipe;
+  pipe.init(reinterpret_cast<uint8_t*>(s_row + kVcSlots), kVcStageBytes, offsets, pool);  // syncs: tables are zeroed
 
-  const int64_t stride = static_cast<int64_t>(gridDim.x) * kVcBlock;
-  for (int64_t base = blockIdx.x * static_cast<int64_t>(kVcBlock); base < n; base += stride) {
-    const int64_t row = base + threadIdx.x;
-    const bool has = row < n;
-    unsigned long long kfp = 0, ktag = 0;
-    const uint8_t* str = pool;
-    uint32_t len = 0;
-    if (has) {
-      int32_t b = __ldg(offsets + row), e = __ldg(offsets + row + 1);
-      if (row_valid(valid, row)) { str = pool + b; len = static_cast<uint32_t>(e - b); }
-      uint64_t fp, tag;
-      fingerprint128(str, len, fp, tag);
-      table_identity(fp, tag, kfp, ktag);
-    }
-    // warp pre-aggregation: a few rounds of "everyone equal to the first pending lane"
-    uint32_t mine = has ? 1u : 0u;
-    unsigned pending = __ballot_sync(0xffffffffu, has);
+  const int64_t ntiles = (n + kVcTileRows - 1) / kVcTileRows;
+  auto tile_end = [&](int64_t t) { return (t + 1) * kVcTileRows < n ? (t + 1) * kVcTileRows : n; };
+  if (threadIdx.x == 0) {  // prologue: the first two tiles of this CTA
+    if (blockIdx.x < ntiles) pipe.issue(blockIdx.x * static_cast<int64_t>(kVcTileRows), tile_end(blockIdx.x), 0);
+    if (blockIdx.x + gridDim.x < ntiles)
+      pipe.issue((blockIdx.x + gridDim.x) * static_cast<int64_t>(kVcTileRows), tile_end(blockIdx.x + gridDim.x), 1);
+  }
+  uint32_t k = 0;
+  for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++k) {
+    const int64_t r0 = tile * kVcTileRows;
+    const int64_t r1 = tile_end(tile);
+    const uint8_t* base = pipe.acquire(k & 1, k >> 1);
 #pragma unroll
-    for (int r = 0; r < kVcAggRounds; ++r) {
-      if (!pending) break;
-      int leader = __ffs(pending) - 1;
-      unsigned long long lfp = __shfl_sync(0xffffffffu, kfp, leader);
-      unsigned long long ltag = __shfl_sync(0xffffffffu, ktag, leader);
-      bool same = has && ((pending >> lane_id()) & 1u) && kfp == lfp && ktag == ltag;
-      unsigned grp = __ballot_sync(0xffffffffu, same);
-      if (static_cast<int>(lane_id()) == leader) mine = __popc(grp);
-      else if (same) mine = 0;
-      pending &= ~grp;
-    }
-    if (mine) {
-      bool done = false;
-      uint32_t idx = static_cast<uint32_t>(home_slot(kfp, kVcSlots - 1));
-#pragma unroll 1
-      for (int p = 0; p < kVcProbes && !done; ++p, idx = (idx + 1) & (kVcSlots - 1)) {
-        unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(&s_fp[idx]);
-        if (cur == 0) {
-          cur = atomicCAS(&s_fp[idx], 0ULL, kfp);
-          if (cur == 0) cur = kfp;
-        }
-        if (cur != kfp) continue;
-        unsigned long long t = *reinterpret_cast<volatile unsigned long long*>(&s_tag[idx]);
-        if (t == 0) {
-          t = atomicCAS(&s_tag[idx], 0ULL, ktag);
-          if (t == 0) { t = ktag; s_row[idx] = static_cast<uint32_t>(row); }
-        }
-        if (t == ktag) { atomicAdd(&s_cnt[idx], mine); done = true; }
+    for (int j = 0; j < kVcRowsPerThread; ++j) {
+      const int64_t row = r0 + j * kVcBlock + threadIdx.x;
+      const bool has = row < r1;
+      StrKey key{0, 0};
+      int32_t b = 0;
+      uint32_t len = 0;
+      if (has) {
+        b = __ldg(offsets + row);
+        int32_t e = __ldg(offsets + row + 1);
+        if (row_valid(valid, row)) len = static_cast<uint32_t>(e - b);
+        key = make_key(base + b, len);
       }
-      if (!done) table_add(table, mask, kfp, ktag, mine, str, len, arena, arena_cap, ctrl);
+      // find (or claim) the term's slot in the front table
+      int slot = -1;
+      if (has) {
+        uint32_t idx = static_cast<uint32_t>(home_slot(key.a, key.b, kVcSlots - 1));
+#pragma unroll 1
+        for (int p = 0; p < kVcProbes; ++p, idx = (idx + 1) & (kVcSlots - 1)) {
+          unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(&s_a[idx]);
+          if (cur == 0) {
+            cur = atomicCAS(&s_a[idx], 0ULL, key.a);
+            if (cur == 0) cur = key.a;
+          }
+          if (cur != key.a) continue;
+          unsigned long long t = *reinterpret_cast<volatile unsigned long long*>(&s_b[idx]);
+          if (t == 0) {
+            t = atomicCAS(&s_b[idx], 0ULL, key.b);
+            if (t == 0) { t = key.b; s_row[idx] = static_cast<uint32_t>(row); }
+          }
+          if (t == key.b) { slot = static_cast<int>(idx); break; }
+        }
+      }
+      // one warp-level aggregation round (absorbs the dominant term), then one atomic per lane
+      const unsigned hits = __ballot_sync(0xffffffffu, slot >= 0);
+      if (hits) {
+        const int leader = __ffs(hits) - 1;
+        const int lslot = __shfl_sync(0xffffffffu, slot, leader);
+        const unsigned grp = __ballot_sync(0xffffffffu, slot == lslot);
+        if (static_cast<int>(lane_id()) == leader) atomicAdd(&s_cnt[lslot], static_cast<uint32_t>(__popc(grp)));
+        else if (slot >= 0 && slot != lslot) atomicAdd(&s_cnt[slot], 1u);
+      }
+      uint32_t code = blockIdx.x * static_cast<uint32_t>(kVcSlots) + static_cast<uint32_t>(slot);
+      if (has && slot < 0)  // front table full around this term: count it in the global table
+        code = kVcLocalCodes + table_add(table, mask, key.a, key.b, 1ULL, pool + b, len, arena, arena_cap, ctrl);
+      if (has && codes != nullptr) __stcs(codes + row, code);  // the row's term, dictionary-encoded
     }
+    __syncthreads();  // everyone is done with this buffer: refill it with the tile after next
+    const int64_t nxt = tile + 2 * static_cast<int64_t>(gridDim.x);
+    if (threadIdx.x == 0 && nxt < ntiles) pipe.issue(nxt * kVcTileRows, tile_end(nxt), k & 1);
   }
   __syncthreads();
   for (int i = threadIdx.x; i < kVcSlots; i += kVcBlock) {  // flush the front table
@@ -134,7 +161,8 @@ __global__ void __launch_bounds__(kVcBlock) vocab_count_kernel(const int32_t* __
       str = pool + b;
       len = static_cast<uint32_t>(offsets[row + 1] - b);
     }
-    table_add(table, mask, s_fp[i], s_tag[i], cnt, str, len, arena, arena_cap, ctrl);
+    uint32_t g = table_add(table, mask, s_a[i], s_b[i], cnt, str, len, arena, arena_cap, ctrl);
+    if (local2global != nullptr) local2global[blockIdx.x * static_cast<uint32_t>(kVcSlots) + i] = g;
   }
 }
 
@@ -144,9 +172,7 @@ __global__ void vocab_insert_kernel(const uint64_t* __restrict__ fp, const uint6
                                     uint8_t* arena, int64_t arena_cap, unsigned long long* ctrl) {
   int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
   if (i >= m) return;
-  unsigned long long kfp, ktag;
-  table_identity(fp[i], tag[i], kfp, ktag);
-  table_add(table, mask, kfp, ktag, count[i], pool + offsets[i], static_cast<uint32_t>(offsets[i + 1] - offsets[i]), arena,
+  table_add(table, mask, fp[i], tag[i], count[i], pool + offsets[i], static_cast<uint32_t>(offsets[i + 1] - offsets[i]), arena,
             arena_cap, ctrl);
 }
 
@@ -168,7 +194,7 @@ __global__ void vocab_compact_kernel(const CountSlot* __restrict__ table, int64_
   unsigned long long cnt = 0;
   if (i < capacity) {
     CountSlot s = table[i];
-    occ = s.fp != 0 && s.tag != 0;
+    occ = s.a != 0 && s.b != 0;
     if (occ) {
       cnt = s.count;
       uint32_t len = static_cast<uint32_t>(s.strref & 0xFFFFFFu);
@@ -195,7 +221,7 @@ __global__ void vocab_export_meta_kernel(const CountSlot* __restrict__ table, co
   int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
   if (i >= m) return;
   CountSlot s = table[ent[i]];
-  fp[i] = s.fp; tag[i] = s.tag; count[i] = s.count;
+  fp[i] = s.a; tag[i] = s.b; count[i] = s.count;
   len[i] = static_cast<int32_t>(s.strref & 0xFFFFFFu);
 }
 
@@ -281,12 +307,12 @@ __global__ void vocab_sort_unpad_kernel(const uint32_t* __restrict__ buf, int64_
   if (i < m) ent[i] = buf[i];
 }
 
-__device__ void lookup_put(LookupSlot* lut, uint64_t mask, unsigned long long kfp, uint32_t tag32, int32_t id) {
-  uint64_t idx = home_slot(kfp, mask);
+__device__ void lookup_put(LookupSlot* lut, uint64_t mask, unsigned long long ka, unsigned long long kb, int32_t id) {
+  uint64_t idx = home_slot(ka, kb, mask);
   for (uint64_t probe = 0; probe <= mask; ++probe, idx = (idx + 1) & mask) {
-    unsigned long long cur = atomicCAS(&lut[idx].fp, 0ULL, kfp);
-    if (cur == 0) {  // claimed an empty slot (equal fingerprints of different terms take separate slots)
-      lut[idx].tag32 = tag32;
+    unsigned long long cur = atomicCAS(&lut[idx].b, 0ULL, kb);  // b is never 0: it marks occupancy
+    if (cur == 0) {
+      lut[idx].a = ka;
       lut[idx].id = id;
       return;
     }
@@ -298,18 +324,46 @@ __global__ void vocab_build_lookup_kernel(const CountSlot* __restrict__ table, c
   int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
   if (i >= k) return;
   CountSlot s = table[ent[i]];
-  lookup_put(lut, mask, s.fp, static_cast<uint32_t>(s.tag), static_cast<int32_t>(i));
+  lookup_put(lut, mask, s.a, s.b, static_cast<int32_t>(i));
 }
 
 __global__ void vocab_lookup_from_terms_kernel(const int32_t* __restrict__ offsets, const uint8_t* __restrict__ pool,
                                                int64_t k, LookupSlot* lut, uint64_t mask) {
   int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
   if (i >= k) return;
-  uint64_t fp, tag;
-  fingerprint128(pool + offsets[i], static_cast<uint32_t>(offsets[i + 1] - offsets[i]), fp, tag);
-  unsigned long long kfp, ktag;
-  table_identity(fp, tag, kfp, ktag);
-  lookup_put(lut, mask, kfp, static_cast<uint32_t>(ktag), static_cast<int32_t>(i));
+  StrKey key = make_key(pool + offsets[i], static_cast<uint32_t>(offsets[i + 1] - offsets[i]));
+  lookup_put(lut, mask, key.a, key.b, static_cast<int32_t>(i));
+}
+
+// Dictionary decode table: for every code the count pass may have written (front-table slots of
+// every CTA, then global slots) the final int64 output of compute_and_apply_vocabulary: the
+// vocabulary id, or vocab_size + Fingerprint64(term) % num_oov_buckets, or default_value.
+__global__ void vocab_final_codes_kernel(const CountSlot* __restrict__ table, int64_t capacity,
+                                         const uint8_t* __restrict__ arena, const uint32_t* __restrict__ local2global,
+                                         const LookupSlot* __restrict__ lut, uint64_t lmask, long long vocab_size,
+                                         long long num_oov, long long dflt, long long* __restrict__ final_code) {
+  int64_t code = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+  if (code >= static_cast<int64_t>(kVcLocalCodes) + capacity) return;
+  uint32_t g = code < kVcLocalCodes ? local2global[code] : static_cast<uint32_t>(code - kVcLocalCodes);
+  if (g == 0xFFFFFFFFu || g >= capacity) return;
+  CountSlot s = table[g];
+  if (s.a == 0 || s.b == 0) return;
+  long long id = -1;
+  uint64_t idx = home_slot(s.a, s.b, lmask);
+  for (uint64_t probe = 0; probe <= lmask; ++probe, idx = (idx + 1) & lmask) {
+    const LookupSlot l = lut[idx];
+    if (l.b == 0) break;
+    if (l.b == s.b && l.a == s.a) { id = l.id; break; }
+  }
+  if (id < 0) {
+    if (num_oov > 0) {
+      uint64_t fp = fingerprint64(arena + (s.strref >> 24), static_cast<uint32_t>(s.strref & 0xFFFFFFu));
+      id = vocab_size + static_cast<long long>(fp % static_cast<uint64_t>(num_oov));
+    } else {
+      id = dflt;
+    }
+  }
+  final_code[code] = id;
 }
 
 static bool pow2(int64_t x) { return x > 0 && (x & (x - 1)) == 0; }
@@ -324,19 +378,44 @@ size_t txf_vocab_table_bytes(int64_t capacity) { return capacity > 0 ? static_ca
 size_t txf_vocab_lookup_bytes(int64_t lookup_cap) { return lookup_cap > 0 ? static_cast<size_t>(lookup_cap) * sizeof(txf::LookupSlot) : 0; }
 size_t txf_vocab_sort_scratch_bytes(int64_t m) { return m > 0 ? static_cast<size_t>(txf::next_pow2(m)) * sizeof(uint32_t) : 0; }
 
+int64_t txf_vocab_local_codes(void) { return txf::kVcLocalCodes; }
+
 int txf_vocab_count(const int32_t* offsets_dev, const uint8_t* pool_dev, const uint8_t* valid_dev, int64_t n, void* table_dev,
-                    int64_t capacity, uint8_t* arena_dev, int64_t arena_cap, uint64_t* ctrl_dev, txf_stream_t stream) {
+                    int64_t capacity, uint8_t* arena_dev, int64_t arena_cap, uint64_t* ctrl_dev, uint32_t* codes_dev,
+                    uint32_t* local2global_dev, txf_stream_t stream) {
   using namespace txf;
   TXF_REQUIRE(n >= 0 && n < (1LL << 31), "vocab_count: n out of range");
   TXF_REQUIRE(pow2(capacity) && capacity < (1LL << 32), "vocab_count: capacity must be a power of two below 2^32");
   TXF_REQUIRE(offsets_dev && pool_dev && table_dev && arena_dev && ctrl_dev && arena_cap > 0, "vocab_count: null pointer");
   TXF_REQUIRE(aligned(table_dev, 32), "vocab_count: table must be 32-byte aligned");
+  TXF_REQUIRE((codes_dev == nullptr) == (local2global_dev == nullptr), "vocab_count: codes and local2global go together");
+  if (local2global_dev != nullptr)
+    TXF_CUDA(cudaMemsetAsync(local2global_dev, 0xFF, static_cast<size_t>(kVcLocalCodes) * sizeof(uint32_t),
+                             static_cast<cudaStream_t>(stream)));
   if (n == 0) return TXF_OK;
-  int64_t want = (n + kVcBlock - 1) / kVcBlock;
-  int grid = static_cast<int>(want < kSMs * 8 ? want : kSMs * 8);
-  vocab_count_kernel<<<grid, kVcBlock, 0, static_cast<cudaStream_t>(stream)>>>(
+  int64_t want = (n + kVcTileRows - 1) / kVcTileRows;
+  int grid = static_cast<int>(want < kSMs ? want : kSMs);
+  TXF_CUDA(cudaFuncSetAttribute(vocab_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kVcSmemBytes)));
+  vocab_count_kernel<<<grid, kVcBlock, kVcSmemBytes, static_cast<cudaStream_t>(stream)>>>(
       offsets_dev, pool_dev, valid_dev, n, static_cast<CountSlot*>(table_dev), static_cast<uint64_t>(capacity - 1), arena_dev,
-      arena_cap, reinterpret_cast<unsigned long long*>(ctrl_dev));
+      arena_cap, reinterpret_cast<unsigned long long*>(ctrl_dev), codes_dev, local2global_dev);
+  TXF_LAUNCH_CHECK();
+  count_launch(1);
+  return TXF_OK;
+}
+
+int txf_vocab_final_codes(const void* table_dev, int64_t capacity, const uint8_t* arena_dev, const uint32_t* local2global_dev,
+                          const void* lookup_dev, int64_t lookup_cap, int64_t vocab_size, int64_t num_oov_buckets,
+                          int64_t default_value, int64_t* final_code_dev, txf_stream_t stream) {
+  using namespace txf;
+  TXF_REQUIRE(pow2(capacity) && capacity < (1LL << 31), "vocab_final_codes: capacity must be a power of two below 2^31");
+  TXF_REQUIRE(pow2(lookup_cap), "vocab_final_codes: lookup_cap must be a power of two");
+  TXF_REQUIRE(table_dev && arena_dev && local2global_dev && lookup_dev && final_code_dev, "vocab_final_codes: null pointer");
+  int64_t total = static_cast<int64_t>(kVcLocalCodes) + capacity;
+  vocab_final_codes_kernel<<<blocks_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const CountSlot*>(table_dev), capacity, arena_dev, local2global_dev, static_cast<const LookupSlot*>(lookup_dev),
+      static_cast<uint64_t>(lookup_cap - 1), vocab_size, num_oov_buckets, default_value,
+      reinterpret_cast<long long*>(final_code_dev));
   TXF_LAUNCH_CHECK();
   count_launch(1);
   return TXF_OK;
@@ -449,7 +528,7 @@ int txf_vocab_build_lookup(const void* table_dev, const uint32_t* ent_sorted_dev
   using namespace txf;
   TXF_REQUIRE(k >= 0, "vocab_build_lookup: negative k");
   TXF_REQUIRE(pow2(lookup_cap) && lookup_cap >= 2 * k && lookup_cap >= 2, "vocab_build_lookup: lookup_cap must be a power of two >= 2k");
-  TXF_REQUIRE(lookup_dev != nullptr && aligned(lookup_dev, 16), "vocab_build_lookup: lookup table null or misaligned");
+  TXF_REQUIRE(lookup_dev != nullptr && aligned(lookup_dev, 8), "vocab_build_lookup: lookup table null or misaligned");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   TXF_CUDA(cudaMemsetAsync(lookup_dev, 0, txf_vocab_lookup_bytes(lookup_cap), s));
   if (k == 0) return TXF_OK;
@@ -467,7 +546,7 @@ int txf_vocab_lookup_from_terms(const int32_t* voc_offsets_dev, const uint8_t* v
   using namespace txf;
   TXF_REQUIRE(k >= 0, "vocab_lookup_from_terms: negative k");
   TXF_REQUIRE(pow2(lookup_cap) && lookup_cap >= 2 * k && lookup_cap >= 2, "vocab_lookup_from_terms: lookup_cap must be a power of two >= 2k");
-  TXF_REQUIRE(lookup_dev != nullptr && aligned(lookup_dev, 16), "vocab_lookup_from_terms: lookup table null or misaligned");
+  TXF_REQUIRE(lookup_dev != nullptr && aligned(lookup_dev, 8), "vocab_lookup_from_terms: lookup table null or misaligned");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   TXF_CUDA(cudaMemsetAsync(lookup_dev, 0, txf_vocab_lookup_bytes(lookup_cap), s));
   if (k == 0) return TXF_OK;

@@ -74,6 +74,9 @@ class TransformState:
     vocabs: Dict[Tuple, VocabResult] = field(default_factory=dict)
     buckets: Dict[int, BucketResult] = field(default_factory=dict)
     num_rows: int = 0
+    # dictionary codes of the analyzed chunks: (vocab key, id(table)) -> (codes int32[n], decode int64[...]).
+    # They alias Engine workspaces and only serve Engine.transform on the very tables that were analyzed.
+    codes: Dict[Tuple, Tuple[torch.Tensor, torch.Tensor]] = field(default_factory=dict)
 
     def mean_var_of(self, key: str):
         return tuple(self.mean_var[self.moment_keys.index(key)].cpu().tolist())
@@ -111,6 +114,7 @@ class Engine:
         self.seed = int(seed)
         self._ws: Dict[Tuple, torch.Tensor] = {}
         self.force_general_quantiles = False
+        self.use_codes = True   # analyze writes dictionary codes; transform of the same table decodes them
         self.last_quantile_path: Dict[int, str] = {}
 
         self.moment_keys: List[str] = []
@@ -188,6 +192,10 @@ class Engine:
             state.buckets[nb] = self._quantiles_finish(nb, pend, chunks, n_total)
         for vk, pend in pending_v.items():
             state.vocabs[vk] = self._vocab_finish(vk, self.vocab_specs[vk], pend)
+            for spec in self.plan.of(VocabSpec):  # decode tables depend on num_oov_buckets / default_value
+                if _vocab_key(spec) == vk:
+                    self._decode_tables(vk, spec, pend, state.vocabs[vk], state)
+                    break
         return state
 
     # -- moments
@@ -404,14 +412,19 @@ class Engine:
         tag = f"v_{spec.in_key}_{spec.top_k}"
         cap = self.vocab_capacity
         table, arena, ctrl, ent, counts = self._vocab_bufs(tag, cap)
-        for ch in chunks:
+        coded = []
+        nlocal = nat.query("txf_vocab_local_codes")
+        for i, ch in enumerate(chunks):
             if len(ch) == 0:
                 continue
             col: StringColumn = ch[spec.in_key]
+            codes = self._buf(f"{tag}_codes{i}", len(ch), torch.int32)
+            l2g = self._buf(f"{tag}_l2g{i}", nlocal, torch.int32)
             nat.call("txf_vocab_count", col.offsets.data_ptr(), col.pool.data_ptr(), _ptr(col.valid), len(ch), table.data_ptr(),
-                     cap, arena.data_ptr(), self.arena_bytes, ctrl.data_ptr(), s)
+                     cap, arena.data_ptr(), self.arena_bytes, ctrl.data_ptr(), codes.data_ptr(), l2g.data_ptr(), s)
+            coded.append((i, id(ch), codes, l2g))
         nat.call("txf_vocab_compact", table.data_ptr(), cap, arena.data_ptr(), ent.data_ptr(), counts.data_ptr(), ctrl.data_ptr(), s)
-        return dict(tag=tag, cap=cap, table=table, arena=arena, ctrl=ctrl, ent=ent, counts=counts)
+        return dict(tag=tag, cap=cap, table=table, arena=arena, ctrl=ctrl, ent=ent, counts=counts, coded=coded)
 
     def _check_vocab_ctrl(self, ctrl_host, spec: VocabSpec):
         if int(ctrl_host[2]) & 2:
@@ -441,6 +454,16 @@ class Engine:
         nat.call("txf_vocab_export_bytes", pend["table"].data_ptr(), pend["arena"].data_ptr(), ent.data_ptr(), m, offsets.data_ptr(),
                  pool.data_ptr(), s)
         return fp, tg, cnt, offsets, pool
+
+    def _decode_tables(self, vk: Tuple, spec: VocabSpec, local, res: VocabResult, state: TransformState):
+        """Per analyzed chunk: code -> final id table, from this rank's OWN count table and the final lookup."""
+        s = self._stream()
+        nlocal = nat.query("txf_vocab_local_codes")
+        for i, table_id, codes, l2g in local["coded"]:
+            final = self._buf(f"{local['tag']}_final{i}", nlocal + local["cap"], torch.int64)
+            nat.call("txf_vocab_final_codes", local["table"].data_ptr(), local["cap"], local["arena"].data_ptr(), l2g.data_ptr(),
+                     res.lookup.data_ptr(), res.lookup_cap, res.size, spec.num_oov_buckets, spec.default_value, final.data_ptr(), s)
+            state.codes[(vk, table_id)] = (codes, final)
 
     def _vocab_finish(self, vk: Tuple, spec: VocabSpec, pend) -> VocabResult:
         s = self._stream()
@@ -550,6 +573,15 @@ class Engine:
             elif isinstance(spec, VocabSpec):
                 res = state.vocabs[_vocab_key(spec)]
                 o = prev.values if prev is not None else torch.empty(n, dtype=torch.int64, device=dev)
+                coded = state.codes.get((_vocab_key(spec), id(table)))
+                first = next(sp for sp in self.plan.of(VocabSpec) if _vocab_key(sp) == _vocab_key(spec))
+                if (coded is not None and coded[0].numel() == n and self.use_codes
+                        and (first.num_oov_buckets, first.default_value) == (spec.num_oov_buckets, spec.default_value)):
+                    op.kind = nat.OP_VOCAB_CODED  # this very table was analyzed: decode its dictionary codes
+                    op.in0, op.p0 = coded[0].data_ptr(), coded[1].data_ptr()
+                    op.out = o.data_ptr()
+                    cols[spec.out_key] = NumericColumn(o)
+                    continue
                 op.kind = nat.OP_VOCAB
                 op.in0, op.valid0, op.pool = col.offsets.data_ptr(), _ptr(col.valid), col.pool.data_ptr()
                 op.p0, op.a0, op.a1, op.a2, op.a3 = res.lookup.data_ptr(), res.lookup_cap, res.size, spec.num_oov_buckets, spec.default_value

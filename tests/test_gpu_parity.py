@@ -136,6 +136,24 @@ def test_synthetic_taxi(ktw, fn, n, force_general):
     check_outputs(out, want, wstate)
 
 
+def test_coded_and_string_vocabulary_paths_agree(ktw, fn):
+    """Transform of the analyzed table decodes dictionary codes; any other table re-reads the term
+    bytes.  Both must give the oracle's ids."""
+    from kubeflow_tfx_workshop_b200 import synth
+    host = synth.taxi_table(123_457, backend="numpy")
+    dev = host.to("cuda")
+    eng = ktw.Engine(ktw.trace(fn, synth.TAXI_SCHEMA))
+    state = eng.analyze(dev)
+    assert len(state.codes) == 2
+    coded = eng.transform(dev, state)
+    eng.use_codes = False
+    plain = eng.transform(dev, state)
+    want, _ = O.analyze_and_transform(helpers.oracle_from_table(host))
+    for k in ("payment_type_xf", "company_xf"):
+        assert np.array_equal(coded[k].values.cpu().numpy(), want[k]), k
+        assert np.array_equal(plain[k].values.cpu().numpy(), want[k]), k
+
+
 def test_synthetic_generators_agree_on_gpu(ktw):
     """torch-on-GPU generator == numpy twin, bit for bit (the benchmark relies on it)."""
     from kubeflow_tfx_workshop_b200 import synth

@@ -164,6 +164,7 @@ def test_device_hash_and_key_logic_compiled_for_host(tmp_path):
 #include <vector>
 #include "common.cuh"
 #include "farmhash.cuh"
+#include "vocab.cuh"
 namespace txf { void set_error(const char*, ...) {} int check_cuda(cudaError_t, const char*) { return 0; } void count_launch(int) {} }
 int main(int argc, char** argv) {
   FILE* f = fopen(argv[1], "rb");
@@ -173,8 +174,8 @@ int main(int argc, char** argv) {
   size_t pos = 8;
   while (pos < 8 + n) {
     unsigned len; memcpy(&len, &buf[pos], 4); pos += 4;
-    uint64_t fp, tag; txf::fingerprint128(&buf[pos], len, fp, tag);
-    printf("%llu\n", (unsigned long long)fp);
+    txf::StrKey k = txf::make_key(&buf[pos], len);
+    printf("%llu %llu %llu\n", (unsigned long long)txf::fingerprint64(&buf[pos], len), k.a, k.b);
     pos += len;
   }
   float probes[] = {-1.5f, -0.0f, 0.0f, 1e-45f, 2.0f};
@@ -187,11 +188,22 @@ int main(int argc, char** argv) {
     subprocess.run(["nvcc", "-O1", "-std=c++17", "-I", csrc, "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
     rng = np.random.default_rng(5)
     items = [bytes(rng.integers(0, 256, L, dtype=np.uint8)) for L in list(range(0, 130)) + [200, 511, 512, 513]]
+    # identity corner cases: NUL padding, a leading 8-byte word of zeros, prefixes of each other
+    items += [b"", b"\0", b"\0\0", b"\0" * 8, b"\0" * 9, b"\0" * 15, b"\0" * 16, b"\x01", b"ab", b"ab\0", b"ab\0\0",
+              b"abcdefgh", b"abcdefgh\0", b"abcdefghi", b"Credit Card", b"Credit Cash", b"x" * 15, b"x" * 16, b"x" * 17]
     blob = b"".join(len(s).to_bytes(4, "little") + s for s in items)
     (tmp_path / "in.bin").write_bytes(blob)
     out = subprocess.run([str(exe), str(tmp_path / "in.bin")], capture_output=True, text=True, check=True).stdout.split("\n")
-    got = [int(x) for x in out[: len(items)]]
+    got = [int(x.split()[0]) for x in out[: len(items)]]
     assert got == [O.fingerprint64_c(s) for s in items]
+    keys128 = [tuple(int(v) for v in x.split()[1:]) for x in out[: len(items)]]
+    assert all(a != 0 and b != 0 for a, b in keys128)                      # 0 marks an unclaimed table slot
+    assert len(set(keys128)) == len(set(items))                            # distinct terms, distinct identities
+    for s_, (a, b) in zip(items, keys128):                                 # terms of <= 15 bytes are stored verbatim
+        if len(s_) <= 15:
+            raw = s_.ljust(16, b"\0")
+            k0, k1 = int.from_bytes(raw[:8], "little"), int.from_bytes(raw[8:], "little") | ((len(s_) + 1) << 56)
+            assert (a, b) == ((k0, k1) if k0 else (1, k1 | (0x40 << 56))), s_
     keys = [l.split() for l in out if l.startswith("K ")]
     probes = np.array([-1.5, -0.0, 0.0, 1e-45, 2.0], np.float32)
     assert [int(k[1]) for k in keys] == O.order_key(probes).tolist()
