@@ -352,7 +352,7 @@ def _slice_col(c, n):
     if c.kind == "numeric":
         return ktw.NumericColumn(c.values[:n], None if c.valid is None else c.valid[: (n + 7) // 8])
     nbytes = int(c.offsets[n].item())
-    return ktw.StringColumn(c.offsets[: n + 1], c.pool[: nbytes + 32], None if c.valid is None else c.valid[: (n + 7) // 8], nbytes)
+    return ktw.StringColumn(c.offsets[: n + 1], c.pool[: nbytes + 64], None if c.valid is None else c.valid[: (n + 7) // 8], nbytes)
 
 
 def _pin(c):

@@ -33,7 +33,7 @@ extern "C" {
 #define TXF_ABI_VERSION 1
 #define TXF_MAX_COLS 16   /* columns handled by one analyzer launch */
 #define TXF_MAX_OPS 32    /* column ops in one fused transform program */
-#define TXF_POOL_SLACK 32 /* readable bytes required past the end of a string pool */
+#define TXF_POOL_SLACK 64 /* readable bytes required past the end of a string pool */
 #define TXF_QMAX_TARGETS 64 /* bracket-count fast path: at most this many boundaries */
 
 enum { TXF_OK = 0, TXF_ERR_ARG = -1, TXF_ERR_CUDA = -2, TXF_ERR_CAPACITY = -3 };

@@ -14,7 +14,7 @@ LIB_PATH = os.path.join(_HERE, "libtaxi_xf.so")
 
 TXF_MAX_COLS = 16
 TXF_MAX_OPS = 32
-TXF_POOL_SLACK = 32
+TXF_POOL_SLACK = 64
 TXF_QMAX_TARGETS = 64
 TXF_F32, TXF_I64 = 0, 1
 (OP_ZSCORE, OP_VOCAB, OP_BUCKETIZE, OP_FILL_I64, OP_FILL_F32, OP_FILL_STR, OP_RATIO_LABEL, OP_VOCAB_CODED) = range(8)

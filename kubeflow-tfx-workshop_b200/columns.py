@@ -20,7 +20,7 @@ from typing import Dict, Iterable, List, Optional, Sequence
 import numpy as np
 import torch
 
-POOL_SLACK = 32
+POOL_SLACK = 64
 FLOAT, INT, BYTES = "float32", "int64", "bytes"
 
 

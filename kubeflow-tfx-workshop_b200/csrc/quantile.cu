@@ -265,12 +265,13 @@ __global__ void qsample_kernel(NumColsView cols, int64_t n, int64_t M, uint64_t 
 }
 
 constexpr int kQBlock = 256;
-constexpr int kQLutBits = 10;            // 1024-entry bin table over [first edge, last edge]
+constexpr int kQLutBits = 12;            // 4096-entry bin table over [first edge, last edge]
 constexpr int kQTileQuads = 2 * kQBlock; // a tile = 2 quads (8 keys) per thread
 constexpr int kQCandBuf = 4096;          // CTA-local candidate buffer (keys); flushed when half full
 
-__device__ __forceinline__ float4 load_quad_as_f32(const void* values, int dtype, int64_t q) {
-  if (dtype == TXF_F32) return ldg_f4(static_cast<const float*>(values) + 4 * q);
+template <bool F32>
+__device__ __forceinline__ float4 load_quad_as_f32(const void* values, int64_t q) {
+  if (F32) return ldg_f4(static_cast<const float*>(values) + 4 * q);
   const long long* v = static_cast<const long long*>(values) + 4 * q;
   longlong2 a = ldg_l2(v), b = ldg_l2(v + 2);
   return make_float4(i64_to_f32(a.x), i64_to_f32(a.y), i64_to_f32(b.x), i64_to_f32(b.y));
@@ -283,6 +284,7 @@ __device__ __forceinline__ float4 load_quad_as_f32(const void* values, int dtype
 // collected in a CTA-local shared-memory buffer and written out in batches, so the streaming
 // loop never waits on a global atomic; the next tile's loads are issued before the current tile
 // is processed.
+template <bool F32>
 __global__ void __launch_bounds__(kQBlock) qcount_kernel(NumColsView cols, int64_t n, int T,
                                                          const uint32_t* __restrict__ edges_all,
                                                          unsigned long long* __restrict__ cells_all,
@@ -292,6 +294,7 @@ __global__ void __launch_bounds__(kQBlock) qcount_kernel(NumColsView cols, int64
   __shared__ uint32_t s_ncand;
   __shared__ unsigned long long s_base;
   const int c = blockIdx.y;
+  if ((cols.dtype[c] == TXF_F32) != F32) return;  // the other instantiation handles this column
   const int E = 2 * T, ncell = 2 * E + 1;
   uint32_t* s_edges = smem;                                                     // [E]
   uint32_t* s_cand = smem + ((E + 1) & ~1);                                     // [kQCandBuf]
@@ -314,36 +317,49 @@ __global__ void __launch_bounds__(kQBlock) qcount_kernel(NumColsView cols, int64
   }
   __syncthreads();
   uint32_t* cand = cand_all + static_cast<size_t>(c) * cand_cap;
+  const void* values = cols.values[c];
+  const uint8_t* __restrict__ valid = cols.valid[c];
   // private 16-bit counter of (cell, thread): lanes of a warp sit in 32 different banks, warps w
   // and w+4 share the words (low/high half), so the read-modify-write never bank-conflicts
   const int my_slot = (((threadIdx.x >> 5) & 3) * 32 + static_cast<int>(lane_id())) * 2 + (threadIdx.x >> 7);
   auto visit = [&](uint32_t key) {
-    int lo;        // number of edges < key
+    const uint32_t d = key - first;  // wraps below the first edge; the table index is clamped, the result overridden
+    uint32_t bin = d >> shift;
+    bin = bin < (1u << kQLutBits) ? bin : (1u << kQLutBits) - 1;
+    uint32_t t = s_lut[bin];
+    t = key < first ? 0u : t;
+    t = key > last ? static_cast<uint32_t>(E) : t;
+    int lo = t & 0x7FFF;  // number of edges < key (exact unless the bin holds edges: then refined)
     bool eq = false;
-    if (key < first) {
-      lo = 0;
-    } else if (key > last) {
-      lo = E;
-    } else {
-      const uint32_t t = s_lut[(key - first) >> shift];
-      lo = t & 0x7FFF;
-      if (t & 0x8000) {
-        while (lo < E && s_edges[lo] < key) ++lo;
-        eq = lo < E && s_edges[lo] == key;
+    if (t & 0x8000) {
+      uint32_t e = s_edges[lo];
+      while (e < key) {
+        if (++lo == E) break;
+        e = s_edges[lo];
       }
+      eq = lo < E && e == key;
     }
     const int cell = 2 * lo + (eq ? 1 : 0);
     s_cnt[cell * kQBlock + my_slot] += 1;      // <= 65535 keys per thread per launch (grid sizing)
-    if ((lo & 1) && !eq) s_cand[atomicAdd(&s_ncand, 1u)] = key;  // strictly inside bracket (lo-1)/2
+    if ((lo & 1) && !eq) {  // strictly inside bracket (lo-1)/2: keep the key
+      const uint32_t pos = atomicAdd(&s_ncand, 1u);
+      if (pos < kQCandBuf) {
+        s_cand[pos] = key;
+      } else {  // CTA buffer full between two flushes (rare): append to the global list directly
+        const unsigned long long g = atomicAdd(&cand_count[c], 1ULL);
+        if (g < static_cast<unsigned long long>(cand_cap)) cand[g] = key;
+      }
+    }
   };
-  auto visit_quad = [&](float4 x, uint32_t m) {
+  auto visit_quad = [&](float4 x, uint32_t vbyte, int64_t q) {  // vbyte: raw bitmap byte of the quad (prefetched)
+    const uint32_t m = valid == nullptr ? 0xFu : (vbyte >> ((4 * q) & 4)) & 0xFu;
     visit(f32_key(m & 1 ? x.x : 0.f)); visit(f32_key(m & 2 ? x.y : 0.f));
     visit(f32_key(m & 4 ? x.z : 0.f)); visit(f32_key(m & 8 ? x.w : 0.f));
   };
   auto flush = [&]() {  // all threads; s_ncand is stable on entry
-    if (threadIdx.x == 0) s_base = atomicAdd(&cand_count[c], static_cast<unsigned long long>(s_ncand));
+    if (threadIdx.x == 0) s_base = atomicAdd(&cand_count[c], static_cast<unsigned long long>(s_ncand < kQCandBuf ? s_ncand : kQCandBuf));
     __syncthreads();
-    const uint32_t m = s_ncand;
+    const uint32_t m = s_ncand < kQCandBuf ? s_ncand : kQCandBuf;
     for (uint32_t i = threadIdx.x; i < m; i += kQBlock) {
       unsigned long long pos = s_base + i;
       if (pos < static_cast<unsigned long long>(cand_cap)) cand[pos] = s_cand[i];
@@ -353,34 +369,36 @@ __global__ void __launch_bounds__(kQBlock) qcount_kernel(NumColsView cols, int64
     __syncthreads();
   };
 
-  const void* values = cols.values[c];
-  const uint8_t* __restrict__ valid = cols.valid[c];
-  const int dtype = cols.dtype[c];
   const int64_t nquads = n >> 2;
   const int64_t ntiles = (nquads + kQTileQuads - 1) / kQTileQuads;
   int64_t tile = blockIdx.x;
   float4 xa = make_float4(0, 0, 0, 0), xb = xa;
-  uint32_t ma = 0, mb = 0;
+  uint32_t va = 0, vb = 0;  // raw validity bytes: decoded at use, so the prefetch never waits on them
+  bool ha = false, hb = false;
   auto load_tile = [&](int64_t t) {
     const int64_t qa = t * kQTileQuads + threadIdx.x, qb = qa + kQBlock;
-    ma = mb = 0x100;  // bit 8 = "no quad here"
-    if (t < ntiles && qa < nquads) { xa = load_quad_as_f32(values, dtype, qa); ma = quad_valid(valid, 4 * qa); }
-    if (t < ntiles && qb < nquads) { xb = load_quad_as_f32(values, dtype, qb); mb = quad_valid(valid, 4 * qb); }
+    ha = t < ntiles && qa < nquads;
+    hb = t < ntiles && qb < nquads;
+    if (ha) { xa = load_quad_as_f32<F32>(values, qa); if (valid) va = __ldg(valid + (qa >> 1)); }
+    if (hb) { xb = load_quad_as_f32<F32>(values, qb); if (valid) vb = __ldg(valid + (qb >> 1)); }
   };
   load_tile(tile);
-  for (; tile < ntiles; tile += gridDim.x) {
+  for (uint32_t it = 1; tile < ntiles; tile += gridDim.x, ++it) {
     const float4 ca = xa, cb = xb;
-    const uint32_t cma = ma, cmb = mb;
+    const uint32_t cva = va, cvb = vb;
+    const bool cha = ha, chb = hb;
+    const int64_t qa = tile * kQTileQuads + threadIdx.x;
     load_tile(tile + gridDim.x);  // prefetch
-    if (!(cma & 0x100)) visit_quad(ca, cma);
-    if (!(cmb & 0x100)) visit_quad(cb, cmb);
-    if (__syncthreads_or(s_ncand > kQCandBuf - 8 * kQBlock)) flush();
+    if (cha) visit_quad(ca, cva, qa);
+    if (chb) visit_quad(cb, cvb, qa + kQBlock);
+    // the CTA buffer is drained every 4 tiles when more than half full (overflow goes to global directly)
+    if ((it & 3) == 0 && __syncthreads_or(s_ncand > kQCandBuf / 2)) flush();
   }
   if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {  // rows past the last full quad
     const int64_t i = (nquads << 2) + threadIdx.x;
     const bool present = row_valid(valid, i);
-    visit(dtype == TXF_F32 ? cell_key_f32(static_cast<const float*>(values)[i], present)
-                           : cell_key_i64(static_cast<const long long*>(values)[i], present));
+    visit(F32 ? cell_key_f32(static_cast<const float*>(values)[i], present)
+              : cell_key_i64(static_cast<const long long*>(values)[i], present));
   }
   __syncthreads();
   flush();
@@ -580,18 +598,30 @@ int txf_qcount(const void* const* values, const uint8_t* const* valid, const int
   if (rc) return rc;
   const int E = 2 * T, ncell = 2 * E + 1;
   size_t smem = static_cast<size_t>((E + 1) & ~1) * 4 + kQCandBuf * 4 + (2u << kQLutBits) + static_cast<size_t>(ncell) * kQBlock * 2;
-  if (smem > 48 * 1024)
-    TXF_CUDA(cudaFuncSetAttribute(qcount_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+  bool any_f32 = false, any_i64 = false;
+  for (int c = 0; c < ncols; ++c) (v.dtype[c] == TXF_F32 ? any_f32 : any_i64) = true;
+  if (smem > 48 * 1024) {
+    TXF_CUDA(cudaFuncSetAttribute(qcount_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    TXF_CUDA(cudaFuncSetAttribute(qcount_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+  }
   int per_sm = static_cast<int>((200 * 1024) / (smem + 1024));
   per_sm = per_sm < 1 ? 1 : (per_sm > 6 ? 6 : per_sm);
   dim3 grid(stream_grid(n, kQBlock, per_sm, ncols), ncols);
   // private 16-bit counters: every thread must see fewer than 65536 keys
   TXF_REQUIRE(n / (static_cast<int64_t>(grid.x) * kQBlock) + 8 < 65536, "qcount: chunk too large for 16-bit counters");
-  qcount_kernel<<<grid, kQBlock, smem, static_cast<cudaStream_t>(stream)>>>(
-      v, n, T, edges_dev, reinterpret_cast<unsigned long long*>(cells_dev), cand_dev,
-      reinterpret_cast<unsigned long long*>(cand_count_dev), cand_cap);
+  if (any_f32) {
+    qcount_kernel<true><<<grid, kQBlock, smem, static_cast<cudaStream_t>(stream)>>>(
+        v, n, T, edges_dev, reinterpret_cast<unsigned long long*>(cells_dev), cand_dev,
+        reinterpret_cast<unsigned long long*>(cand_count_dev), cand_cap);
+    count_launch(1);
+  }
+  if (any_i64) {
+    qcount_kernel<false><<<grid, kQBlock, smem, static_cast<cudaStream_t>(stream)>>>(
+        v, n, T, edges_dev, reinterpret_cast<unsigned long long*>(cells_dev), cand_dev,
+        reinterpret_cast<unsigned long long*>(cand_count_dev), cand_cap);
+    count_launch(1);
+  }
   TXF_LAUNCH_CHECK();
-  count_launch(1);
   return TXF_OK;
 }
 

@@ -20,7 +20,7 @@ constexpr int kXfBlock = 1024;
 constexpr int kXfUnroll = 4;                                   // quads in flight per thread and op
 constexpr int64_t kXfTileRows = 4LL * kXfBlock * kXfUnroll;    // 16384 rows per tile
 constexpr int kXfStageBytes = 48 * 1024;                       // per buffer: staged term bytes of one vocabulary tile
-constexpr int kXfPipeBytes = StrTilePipe::header_bytes() + 2 * kXfStageBytes;
+constexpr int kXfPipeBytes = (StrTilePipe::smem_bytes(kXfStageBytes, 2 * kXfBlock) + 15) & ~15;
 constexpr int kXfVocabTileRows = 2 * kXfBlock;
 constexpr int kXfSmemBudget = 200 * 1024;
 
@@ -339,7 +339,7 @@ __device__ __forceinline__ void run_vocab(const XfOp& op, const uint8_t* smem, u
   const long long vocab_size = op.a1, num_oov = op.a2, dflt = op.a3;
   long long* out = static_cast<long long*>(op.out);
   StrTilePipe pipe;
-  pipe.init(stage, kXfStageBytes, off, pool);
+  pipe.init(stage, kXfStageBytes, kXfVocabTileRows, off, pool, valid, n);
   const int64_t ntiles = (n + kXfVocabTileRows - 1) / kXfVocabTileRows;
   auto tile_end = [&](int64_t t) { return (t + 1) * kXfVocabTileRows < n ? (t + 1) * kXfVocabTileRows : n; };
   if (threadIdx.x == 0) {

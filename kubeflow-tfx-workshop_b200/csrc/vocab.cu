@@ -17,15 +17,16 @@
 
 namespace txf {
 
-constexpr int kVcBlock = 1024;            // one persistent CTA per SM
-constexpr int kVcSlots = 4096;            // shared-memory front table: 4096 x 24 B = 96 KB
+constexpr int kVcBlock = 512;             // two persistent CTAs per SM: one computes while the other waits at a barrier
+constexpr int kVcSlots = 2048;            // shared-memory front table per CTA: 2048 x 24 B = 48 KB
 constexpr int kVcProbes = 8;
 constexpr int kVcRowsPerThread = 2;
 constexpr int kVcTileRows = kVcBlock * kVcRowsPerThread;
-constexpr int kVcStageBytes = 56 * 1024;  // per buffer: staged term bytes of one tile (avg 16 B/row -> 32 KB)
-constexpr size_t kVcSmemBytes = kVcSlots * (8 + 8 + 4 + 4) + StrTilePipe::header_bytes() + 2 * kVcStageBytes;
+constexpr int kVcStageBytes = 24 * 1024;  // per buffer: staged term bytes of one tile (avg 16 B/row -> 16 KB)
+constexpr size_t kVcSmemBytes = kVcSlots * (8 + 8 + 4 + 4) + kVcTileRows * 2 + StrTilePipe::smem_bytes(kVcStageBytes, kVcTileRows);
 constexpr uint32_t kPadEnt = 0xFFFFFFFFu;
-constexpr uint32_t kVcLocalCodes = kSMs * kVcSlots;  // codes below this: (CTA, front-table slot); above: global slot
+constexpr int kVcGrid = 2 * kSMs;
+constexpr uint32_t kVcLocalCodes = kVcGrid * kVcSlots;  // codes below this: (CTA, front-table slot); above: global slot
 
 __device__ __forceinline__ unsigned long long ldcg64(const unsigned long long* p) {
   return __ldcg(p);  // L2 only: never a stale L1 line for words other SMs update atomically
@@ -70,7 +71,122 @@ __device__ uint32_t table_add(CountSlot* table, uint64_t mask, unsigned long lon
   return 0xFFFFFFFFu;
 }
 
-__global__ void __launch_bounds__(kVcBlock, 1) vocab_count_kernel(const int32_t* __restrict__ offsets,
+// Front-table state of one CTA (shared memory) plus what a row needs to be counted.
+struct VcFront {
+  unsigned long long* s_a;
+  unsigned long long* s_b;
+  uint32_t* s_cnt;
+  uint32_t* s_row;
+  CountSlot* table;
+  uint64_t mask;
+  uint8_t* arena;
+  int64_t arena_cap;
+  unsigned long long* ctrl;
+  uint32_t* codes;
+  const uint8_t* pool;
+};
+
+// Slow path of the front-table search: full claim protocol (CAS on word a, then on word b) over
+// up to kVcProbes slots.  Kept out of line so the common "already there" case stays straight-line.
+__device__ __noinline__ int vc_find_slow(unsigned long long* s_a, unsigned long long* s_b, uint32_t* s_row,
+                                         unsigned long long ka, unsigned long long kb, uint32_t idx, uint32_t row) {
+  struct { unsigned long long *s_a, *s_b; uint32_t* s_row; } f{s_a, s_b, s_row};
+  const StrKey key{ka, kb};
+  for (int p = 0; p < kVcProbes; ++p, idx = (idx + 1) & (kVcSlots - 1)) {
+    unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(&f.s_a[idx]);
+    if (cur == 0) {
+      cur = atomicCAS(&f.s_a[idx], 0ULL, key.a);
+      if (cur == 0) cur = key.a;
+    }
+    if (cur != key.a) continue;
+    unsigned long long t = *reinterpret_cast<volatile unsigned long long*>(&f.s_b[idx]);
+    if (t == 0) {
+      t = atomicCAS(&f.s_b[idx], 0ULL, key.b);
+      if (t == 0) { t = key.b; f.s_row[idx] = row; }
+    }
+    if (t == key.b) return static_cast<int>(idx);
+  }
+  return -1;
+}
+
+// Count one term per lane (has == false: the lane only takes part in the warp votes).  Must be
+// called by all 32 lanes of a warp together.
+__device__ __forceinline__ void vc_count(const VcFront& f, bool has, StrKey key, int64_t row, int32_t b, uint32_t len) {
+  int slot = -1;
+  if (has) {
+    const uint32_t idx = static_cast<uint32_t>(home_slot(key.a, key.b, kVcSlots - 1));
+    // fast path: the term already sits in its home slot (both words are written before any count)
+    const unsigned long long a0 = *reinterpret_cast<volatile unsigned long long*>(&f.s_a[idx]);
+    const unsigned long long b0 = *reinterpret_cast<volatile unsigned long long*>(&f.s_b[idx]);
+    slot = (a0 == key.a && b0 == key.b) ? static_cast<int>(idx)
+                                        : vc_find_slow(f.s_a, f.s_b, f.s_row, key.a, key.b, idx, static_cast<uint32_t>(row));
+  }
+  // one warp-level aggregation round (absorbs the dominant term), then one atomic per lane
+  const unsigned hits = __ballot_sync(0xffffffffu, slot >= 0);
+  if (hits) {
+    const int leader = __ffs(hits) - 1;
+    const int lslot = __shfl_sync(0xffffffffu, slot, leader);
+    const unsigned grp = __ballot_sync(0xffffffffu, slot == lslot);
+    if (static_cast<int>(lane_id()) == leader) atomicAdd(&f.s_cnt[lslot], static_cast<uint32_t>(__popc(grp)));
+    else if (slot >= 0 && slot != lslot) atomicAdd(&f.s_cnt[slot], 1u);
+  }
+  uint32_t code = blockIdx.x * static_cast<uint32_t>(kVcSlots) + static_cast<uint32_t>(slot);
+  if (has && slot < 0)  // front table full around this term: count it in the global table
+    code = kVcLocalCodes + table_add(f.table, f.mask, key.a, key.b, 1ULL, f.pool + b, len, f.arena, f.arena_cap, f.ctrl);
+  if (has && f.codes != nullptr) __stcs(f.codes + row, code);  // the row's term, dictionary-encoded
+}
+
+// One tile: phase A counts the short terms (exact identity, a handful of instructions) and
+// queues the long ones; phase B hashes the queued terms with all lanes busy -- columns that mix
+// empty/short and long terms would otherwise idle most lanes of a warp during the hashing.
+template <bool STAGED, bool META>
+__device__ __forceinline__ void vc_tile(const VcFront& f, const TileRows<META> rows, const uint8_t* base, int64_t r0, int64_t r1,
+                                        uint16_t* s_queue, uint32_t* s_nq, const uint4* s_mask) {
+  const uint32_t sbase = STAGED ? smem_u32(base + rows.begin(r0)) - static_cast<uint32_t>(rows.begin(r0)) : 0u;
+#pragma unroll
+  for (int j = 0; j < kVcRowsPerThread; ++j) {
+    const int64_t row = r0 + j * kVcBlock + threadIdx.x;
+    const bool in_tile = row < r1;
+    int32_t b = 0;
+    uint32_t len = 0;
+    if (in_tile) {
+      b = rows.begin(row);
+      if (rows.present(row)) len = static_cast<uint32_t>(rows.end(row) - b);
+    }
+    const bool is_long = in_tile && len > kExactKeyMax;
+    StrKey key{0, 0};
+    if (in_tile && !is_long)
+      key = STAGED ? make_key_exact_smem(sbase + static_cast<uint32_t>(b), len, s_mask) : make_key_exact(PtrFetch{base + b}, len);
+    const unsigned lm = __ballot_sync(0xffffffffu, is_long);
+    if (lm) {  // queue the long rows of this warp (one shared atomic per warp)
+      uint32_t qb = 0;
+      const int leader = __ffs(lm) - 1;
+      if (static_cast<int>(lane_id()) == leader) qb = atomicAdd(s_nq, static_cast<uint32_t>(__popc(lm)));
+      qb = __shfl_sync(0xffffffffu, qb, leader);
+      if (is_long) s_queue[qb + __popc(lm & ((1u << lane_id()) - 1u))] = static_cast<uint16_t>(row - r0);
+    }
+    vc_count(f, in_tile && !is_long, key, row, b, len);
+  }
+  __syncthreads();
+  const uint32_t nq = *s_nq;
+  for (uint32_t t0 = 0; t0 < nq; t0 += kVcBlock) {  // block-uniform trip count
+    const uint32_t t = t0 + threadIdx.x;
+    const bool has = t < nq;
+    int64_t row = r0;
+    int32_t b = 0;
+    uint32_t len = 0;
+    StrKey key{0, 0};
+    if (has) {
+      row = r0 + s_queue[t];
+      b = rows.begin(row);
+      len = static_cast<uint32_t>(rows.end(row) - b);
+      key = STAGED ? make_key_hashed_smem(sbase + static_cast<uint32_t>(b), len) : make_key_hashed(PtrFetch{base + b}, len);
+    }
+    vc_count(f, has, key, row, b, len);
+  }
+}
+
+__global__ void __launch_bounds__(kVcBlock, 2) vocab_count_kernel(const int32_t* __restrict__ offsets,
                                                                   const uint8_t* __restrict__ pool,
                                                                   const uint8_t* __restrict__ valid, int64_t n,
                                                                   CountSlot* table, uint64_t mask, uint8_t* arena,
@@ -78,13 +194,20 @@ __global__ void __launch_bounds__(kVcBlock, 1) vocab_count_kernel(const int32_t*
                                                                   uint32_t* __restrict__ codes,
                                                                   uint32_t* __restrict__ local2global) {
   extern __shared__ __align__(16) uint8_t vc_smem[];
-  unsigned long long* s_a = reinterpret_cast<unsigned long long*>(vc_smem);
-  unsigned long long* s_b = s_a + kVcSlots;
-  uint32_t* s_cnt = reinterpret_cast<uint32_t*>(s_b + kVcSlots);
-  uint32_t* s_row = s_cnt + kVcSlots;
-  for (int i = threadIdx.x; i < kVcSlots; i += kVcBlock) { s_a[i] = 0; s_b[i] = 0; s_cnt[i] = 0; s_row[i] = 0; }
+  __shared__ uint32_t s_nq;
+  __shared__ uint4 s_mask[16];
+  fill_short_masks(s_mask);
+  VcFront f;
+  f.s_a = reinterpret_cast<unsigned long long*>(vc_smem);
+  f.s_b = f.s_a + kVcSlots;
+  f.s_cnt = reinterpret_cast<uint32_t*>(f.s_b + kVcSlots);
+  f.s_row = f.s_cnt + kVcSlots;
+  uint16_t* s_queue = reinterpret_cast<uint16_t*>(f.s_row + kVcSlots);  // [kVcTileRows]
+  f.table = table; f.mask = mask; f.arena = arena; f.arena_cap = arena_cap; f.ctrl = ctrl; f.codes = codes; f.pool = pool;
+  for (int i = threadIdx.x; i < kVcSlots; i += kVcBlock) { f.s_a[i] = 0; f.s_b[i] = 0; f.s_cnt[i] = 0; f.s_row[i] = 0; }
+  if (threadIdx.x == 0) s_nq = 0;
   StrTilePipe pipe;
-  pipe.init(reinterpret_cast<uint8_t*>(s_row + kVcSlots), kVcStageBytes, offsets, pool);  // syncs: tables are zeroed
+  pipe.init(reinterpret_cast<uint8_t*>(s_queue + kVcTileRows), kVcStageBytes, kVcTileRows, offsets, pool, valid, n);  // syncs
 
   const int64_t ntiles = (n + kVcTileRows - 1) / kVcTileRows;
   auto tile_end = [&](int64_t t) { return (t + 1) * kVcTileRows < n ? (t + 1) * kVcTileRows : n; };
@@ -98,62 +221,25 @@ __global__ void __launch_bounds__(kVcBlock, 1) vocab_count_kernel(const int32_t*
     const int64_t r0 = tile * kVcTileRows;
     const int64_t r1 = tile_end(tile);
     const uint8_t* base = pipe.acquire(k & 1, k >> 1);
-#pragma unroll
-    for (int j = 0; j < kVcRowsPerThread; ++j) {
-      const int64_t row = r0 + j * kVcBlock + threadIdx.x;
-      const bool has = row < r1;
-      StrKey key{0, 0};
-      int32_t b = 0;
-      uint32_t len = 0;
-      if (has) {
-        b = __ldg(offsets + row);
-        int32_t e = __ldg(offsets + row + 1);
-        if (row_valid(valid, row)) len = static_cast<uint32_t>(e - b);
-        key = make_key(base + b, len);
-      }
-      // find (or claim) the term's slot in the front table
-      int slot = -1;
-      if (has) {
-        uint32_t idx = static_cast<uint32_t>(home_slot(key.a, key.b, kVcSlots - 1));
-#pragma unroll 1
-        for (int p = 0; p < kVcProbes; ++p, idx = (idx + 1) & (kVcSlots - 1)) {
-          unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(&s_a[idx]);
-          if (cur == 0) {
-            cur = atomicCAS(&s_a[idx], 0ULL, key.a);
-            if (cur == 0) cur = key.a;
-          }
-          if (cur != key.a) continue;
-          unsigned long long t = *reinterpret_cast<volatile unsigned long long*>(&s_b[idx]);
-          if (t == 0) {
-            t = atomicCAS(&s_b[idx], 0ULL, key.b);
-            if (t == 0) { t = key.b; s_row[idx] = static_cast<uint32_t>(row); }
-          }
-          if (t == key.b) { slot = static_cast<int>(idx); break; }
-        }
-      }
-      // one warp-level aggregation round (absorbs the dominant term), then one atomic per lane
-      const unsigned hits = __ballot_sync(0xffffffffu, slot >= 0);
-      if (hits) {
-        const int leader = __ffs(hits) - 1;
-        const int lslot = __shfl_sync(0xffffffffu, slot, leader);
-        const unsigned grp = __ballot_sync(0xffffffffu, slot == lslot);
-        if (static_cast<int>(lane_id()) == leader) atomicAdd(&s_cnt[lslot], static_cast<uint32_t>(__popc(grp)));
-        else if (slot >= 0 && slot != lslot) atomicAdd(&s_cnt[slot], 1u);
-      }
-      uint32_t code = blockIdx.x * static_cast<uint32_t>(kVcSlots) + static_cast<uint32_t>(slot);
-      if (has && slot < 0)  // front table full around this term: count it in the global table
-        code = kVcLocalCodes + table_add(table, mask, key.a, key.b, 1ULL, pool + b, len, arena, arena_cap, ctrl);
-      if (has && codes != nullptr) __stcs(codes + row, code);  // the row's term, dictionary-encoded
-    }
+    const int bsel = k & 1;
+    if (pipe.staged[bsel] && pipe.meta[bsel])
+      vc_tile<true, true>(f, tile_rows_of<true>(pipe, bsel, r0), base, r0, r1, s_queue, &s_nq, s_mask);
+    else if (pipe.staged[bsel])
+      vc_tile<true, false>(f, tile_rows_of<false>(pipe, bsel, r0), base, r0, r1, s_queue, &s_nq, s_mask);
+    else
+      vc_tile<false, false>(f, tile_rows_of<false>(pipe, bsel, r0), base, r0, r1, s_queue, &s_nq, s_mask);
     __syncthreads();  // everyone is done with this buffer: refill it with the tile after next
     const int64_t nxt = tile + 2 * static_cast<int64_t>(gridDim.x);
-    if (threadIdx.x == 0 && nxt < ntiles) pipe.issue(nxt * kVcTileRows, tile_end(nxt), k & 1);
+    if (threadIdx.x == 0) {
+      s_nq = 0;
+      if (nxt < ntiles) pipe.issue(nxt * kVcTileRows, tile_end(nxt), k & 1);
+    }
   }
   __syncthreads();
   for (int i = threadIdx.x; i < kVcSlots; i += kVcBlock) {  // flush the front table
-    uint32_t cnt = s_cnt[i];
+    uint32_t cnt = f.s_cnt[i];
     if (!cnt) continue;
-    int64_t row = s_row[i];
+    int64_t row = f.s_row[i];
     const uint8_t* str = pool;
     uint32_t len = 0;
     if (row_valid(valid, row)) {
@@ -161,7 +247,7 @@ __global__ void __launch_bounds__(kVcBlock, 1) vocab_count_kernel(const int32_t*
       str = pool + b;
       len = static_cast<uint32_t>(offsets[row + 1] - b);
     }
-    uint32_t g = table_add(table, mask, s_a[i], s_b[i], cnt, str, len, arena, arena_cap, ctrl);
+    uint32_t g = table_add(table, mask, f.s_a[i], f.s_b[i], cnt, str, len, arena, arena_cap, ctrl);
     if (local2global != nullptr) local2global[blockIdx.x * static_cast<uint32_t>(kVcSlots) + i] = g;
   }
 }
@@ -394,7 +480,7 @@ int txf_vocab_count(const int32_t* offsets_dev, const uint8_t* pool_dev, const u
                              static_cast<cudaStream_t>(stream)));
   if (n == 0) return TXF_OK;
   int64_t want = (n + kVcTileRows - 1) / kVcTileRows;
-  int grid = static_cast<int>(want < kSMs ? want : kSMs);
+  int grid = static_cast<int>(want < kVcGrid ? want : kVcGrid);
   TXF_CUDA(cudaFuncSetAttribute(vocab_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kVcSmemBytes)));
   vocab_count_kernel<<<grid, kVcBlock, kVcSmemBytes, static_cast<cudaStream_t>(stream)>>>(
       offsets_dev, pool_dev, valid_dev, n, static_cast<CountSlot*>(table_dev), static_cast<uint64_t>(capacity - 1), arena_dev,

@@ -1,0 +1,80 @@
+"""Multi-GPU parity check, launched by torchrun (one rank per GPU):
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+        tests/multi_gpu_check.py [rows]
+
+Every rank analyzes its contiguous row shard, the partial states are merged over NCCL, every rank
+transforms its shard; rank 0 checks state and outputs against the oracle run on ALL rows, and
+that every rank ended with the same state.
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+
+def main():
+    n = int(sys.argv[1]) if len(sys.argv) > 1 else 700_001
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    import helpers
+    from helpers import O
+    import kubeflow_tfx_workshop_b200 as ktw
+    from kubeflow_tfx_workshop_b200 import synth
+
+    fn = helpers.load_example_preprocessing_fn(ktw).preprocessing_fn
+    comm = ktw.Comm()
+    lo, hi = ktw.shard_range(n, rank, world)
+    shard_host = synth.taxi_table(hi - lo, lo, backend="numpy")
+    for force_general in (False, True):
+        eng = ktw.Engine(ktw.trace(fn, synth.TAXI_SCHEMA), device=f"cuda:{local}", comm=comm)
+        eng.force_general_quantiles = force_general
+        out, state = eng.analyze_and_transform(shard_host.to(f"cuda:{local}"))
+        torch.cuda.synchronize()
+        # identical state on every rank
+        sig = []
+        for k in state.moment_keys:
+            sig += list(state.mean_var_of(k))
+        for nb, res in state.buckets.items():
+            for k in res.keys:
+                sig += res.boundaries_of(k).astype(np.float64).tolist()
+        for key, res in state.vocabs.items():
+            sig += [float(res.size), float(sum(len(t) for t in res.terms()))]
+        t = torch.tensor(sig, dtype=torch.float64, device=f"cuda:{local}")
+        g = comm.all_gather(t)
+        assert bool((g == g[0]).all()), "analyzer state differs between ranks"
+        # parity of this rank's shard against the oracle over ALL rows (recomputed per rank: small n)
+        whole = synth.taxi_table(n, backend="numpy")
+        want, wstate = O.analyze_and_transform(helpers.oracle_from_table(whole))
+        for k, (mean, var) in wstate["zscore"].items():
+            m, v = state.mean_var_of(k)
+            assert abs(m - float(mean)) <= 1e-6 * abs(float(mean)) and abs(v - float(var)) <= 1e-6 * abs(float(var)), k
+        for key, res in state.vocabs.items():
+            assert res.terms() == wstate["vocab"][key[0]], key
+        for nb, res in state.buckets.items():
+            for k in res.keys:
+                assert np.array_equal(res.boundaries_of(k).view(np.uint32), wstate["boundaries"][k].view(np.uint32)), k
+        for key, w in want.items():
+            col = out[key]
+            if isinstance(w, list):
+                assert col.to_list() == w[lo:hi], key
+            elif w.dtype == np.float32:
+                mean, var = wstate["zscore"][key[:-3]]
+                assert helpers.zscore_close(col.values.cpu().numpy(), w[lo:hi], mean, var), key
+            else:
+                assert np.array_equal(col.values.cpu().numpy(), w[lo:hi]), key
+        if rank == 0:
+            print(f"multi-gpu parity ok: world={world} rows={n} quantile path={eng.last_quantile_path}", flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
