@@ -188,6 +188,8 @@ class Engine:
         pending_v = {vk: self._vocab_count(vk, spec, chunks) for vk, spec in self.vocab_specs.items()}
         # one host round trip: everything queued above has to finish before sizes/flags are read
         torch.cuda.current_stream().synchronize()
+        if self.comm.active:
+            self._exchange(pending_q, pending_v)
         for nb, pend in pending_q.items():
             state.buckets[nb] = self._quantiles_finish(nb, pend, chunks, n_total)
         for vk, pend in pending_v.items():
@@ -345,6 +347,80 @@ class Engine:
                  nbound.data_ptr(), s)
         pend.update(status=status, bounds=bounds, nbound=nbound)
 
+    def _exchange(self, pending_q, pending_v):
+        """Merge the per-rank analyzer partials (the one real exchange step of the path) with a
+        handful of collectives: one all-gather of every size, one all-reduce of the cell counts and
+        one padded all-gather of the candidate keys per bucket group, one packed all-gather of the
+        vocabulary entries per vocabulary.  Results land back in the pending dicts."""
+        dev, W = self.device, self.comm.world
+        s = self._stream()
+        fast = [(nb, p) for nb, p in pending_q.items() if p["fast"]]
+        voc = list(pending_v.items())
+        # vocabulary entries of this rank, serialised on the device (sizes known after the sync above)
+        for vk, p in voc:
+            kept = int(p["ctrl"][3].item())
+            p["kept_local"] = kept
+            p["export"] = self._export_entries(p, p["ent"], kept)
+        sizes = [p["cand_count"] for _, p in fast]
+        for vk, p in voc:
+            sizes.append(torch.tensor([p["kept_local"]], dtype=torch.int64, device=dev))
+            sizes.append(p["export"][3][-1:].clone())  # bytes of the exported terms
+        if not sizes:
+            return
+        all_sizes = self.comm.all_gather(torch.cat(sizes)).cpu()  # [W, K] -- the second (and last but one) host sync
+        k = 0
+        for nb, p in fast:
+            ncols = len(p["keys"])
+            counts = all_sizes[:, k:k + ncols]
+            k += ncols
+            self.comm.all_reduce_sum_(p["cells"])
+            if int(counts.max()) > p["cand_cap"]:
+                p["fast"] = False  # some rank overflowed its candidate buffer: every rank falls back
+                continue
+            mx = max(int(counts.max()), 1)
+            g = self.comm.all_gather(p["cand"][:, :mx].contiguous())  # [W, ncols, mx]
+            tot = counts.sum(dim=0).tolist()
+            cap = max(max(tot), 1)
+            cand = self._buf(f"q{nb}_cand_merged", (ncols, cap), torch.int32)
+            for c in range(ncols):
+                torch.cat([g[r, c, : int(counts[r, c])] for r in range(W)], out=cand[c, : tot[c]])
+            count = torch.tensor(tot, dtype=torch.int64, device=dev)
+            p.update(cand=cand, cand_count=count, cand_cap=cap)
+            self._quantiles_resolve(nb, p)
+        for vk, p in voc:
+            kepts = all_sizes[:, k].tolist()
+            nbytes = all_sizes[:, k + 1].tolist()
+            k += 2
+            fp, tg, cnt, offsets, pool = p["export"]
+            kmax, bmax = max(max(kepts), 1), (max(max(nbytes), 1) + 7) // 8 * 8  # rows of the gathered matrix stay 8-byte aligned
+            lens = torch.zeros(kmax, dtype=torch.int64, device=dev)
+            kl = p["kept_local"]
+            if kl:
+                lens[:kl] = offsets[1:kl + 1] - offsets[:kl]
+            pad8 = lambda t: torch.cat([t[:kl], torch.zeros(kmax - kl, dtype=torch.int64, device=dev)]).view(torch.uint8)
+            packed = torch.cat([pad8(fp), pad8(tg), pad8(cnt), lens.view(torch.uint8),
+                                pool[: nbytes[self.comm.rank]], torch.zeros(bmax - nbytes[self.comm.rank], dtype=torch.uint8, device=dev)])
+            g = self.comm.all_gather(packed)  # [W, 32*kmax + bmax]
+            col = lambda r, j: g[r, 8 * kmax * j: 8 * kmax * (j + 1)].view(torch.int64)[: kepts[r]]
+            g_fp = torch.cat([col(r, 0) for r in range(W)])
+            g_tg = torch.cat([col(r, 1) for r in range(W)])
+            g_cnt = torch.cat([col(r, 2) for r in range(W)])
+            g_len = torch.cat([col(r, 3) for r in range(W)])
+            g_pool = torch.cat([g[r, 32 * kmax: 32 * kmax + nbytes[r]] for r in range(W)] +
+                               [torch.zeros(nat.TXF_POOL_SLACK, dtype=torch.uint8, device=dev)])
+            m = int(g_fp.numel())
+            g_off = torch.zeros(m + 1, dtype=torch.int64, device=dev)
+            if m:
+                torch.cumsum(g_len, 0, out=g_off[1:])
+            cap2 = max(self.vocab_capacity, _pow2_at_least(2 * max(m, 1)))
+            tag2 = p["tag"] + "_merged"
+            table, arena, ctrl, ent, counts_buf = self._vocab_bufs(tag2, cap2)
+            nat.call("txf_vocab_insert", g_fp.data_ptr(), g_tg.data_ptr(), g_cnt.data_ptr(), g_off.data_ptr(), g_pool.data_ptr(), m,
+                     table.data_ptr(), cap2, arena.data_ptr(), self.arena_bytes, ctrl.data_ptr(), s)
+            nat.call("txf_vocab_compact", table.data_ptr(), cap2, arena.data_ptr(), ent.data_ptr(), counts_buf.data_ptr(),
+                     ctrl.data_ptr(), s)
+            p["merged"] = dict(tag=tag2, cap=cap2, table=table, arena=arena, ctrl=ctrl, ent=ent, counts=counts_buf)
+
     def _quantiles_general(self, nb: int, keys: List[str], chunks, n_total: int) -> BucketResult:
         """Exact radix select over the whole column (any number of boundaries)."""
         T = nb - 1
@@ -372,24 +448,6 @@ class Engine:
             self.last_quantile_path[nb] = "empty"
             return BucketResult(list(keys), nb, torch.zeros((ncols, max(T, 1)), dtype=torch.float32, device=self.device),
                                 torch.zeros((ncols,), dtype=torch.int32, device=self.device), path="empty")
-        if pend["fast"] and self.comm.active:
-            # merge per-rank cell counts (sum) and candidate keys (concatenation), then resolve
-            cc = pend["cand_count"].cpu().tolist()
-            overflow = torch.tensor([1 if max(cc) > pend["cand_cap"] else 0], dtype=torch.int64, device=self.device)
-            self.comm.all_reduce_max_(overflow)
-            self.comm.all_reduce_sum_(pend["cells"])
-            if int(overflow.item()) == 0:
-                merged = [self.comm.all_gather_var(pend["cand"][c], int(cc[c]))[0] for c in range(ncols)]
-                cap = max(max(int(m.numel()) for m in merged), 1)
-                cand = self._buf(f"q{nb}_cand_merged", (ncols, cap), torch.int32)
-                count = self._buf(f"q{nb}_cand_count_merged", (ncols,), torch.int64)
-                for c, m in enumerate(merged):
-                    cand[c, : m.numel()] = m
-                    count[c] = m.numel()
-                pend.update(cand=cand, cand_count=count, cand_cap=cap)
-                self._quantiles_resolve(nb, pend)
-            else:
-                pend["fast"] = False
         if pend["fast"]:
             status = pend["status"].cpu()
             if int(status.abs().sum()) == 0:
@@ -471,29 +529,8 @@ class Engine:
         self._check_vocab_ctrl(ctrl_host, spec)
         kept = int(ctrl_host[3])
         if self.comm.active:
-            # exchange the admitted entries of every rank and rebuild one merged table everywhere
-            fp, tg, cnt, offsets, pool = self._export_entries(pend, pend["ent"], kept)
-            nbytes = int(offsets[-1].item())
-            g_fp, counts = self.comm.all_gather_var(fp, kept)
-            g_tg, _ = self.comm.all_gather_var(tg, kept)
-            g_cnt, _ = self.comm.all_gather_var(cnt, kept)
-            lens = (offsets[1:] - offsets[:-1]).contiguous() if kept else torch.zeros(0, dtype=torch.int64, device=self.device)
-            g_len, _ = self.comm.all_gather_var(lens, kept)
-            g_pool, _ = self.comm.all_gather_var(pool, nbytes)
-            m = int(g_fp.numel())
-            g_off = torch.zeros(m + 1, dtype=torch.int64, device=self.device)
-            if m:
-                torch.cumsum(g_len, 0, out=g_off[1:])
-            g_pool = torch.cat([g_pool, torch.zeros(nat.TXF_POOL_SLACK, dtype=torch.uint8, device=self.device)])
-            cap2 = max(self.vocab_capacity, _pow2_at_least(2 * max(m, 1)))
-            tag2 = pend["tag"] + "_merged"
-            table, arena, ctrl, ent, counts_buf = self._vocab_bufs(tag2, cap2)
-            nat.call("txf_vocab_insert", g_fp.data_ptr(), g_tg.data_ptr(), g_cnt.data_ptr(), g_off.data_ptr(), g_pool.data_ptr(), m,
-                     table.data_ptr(), cap2, arena.data_ptr(), self.arena_bytes, ctrl.data_ptr(), s)
-            nat.call("txf_vocab_compact", table.data_ptr(), cap2, arena.data_ptr(), ent.data_ptr(), counts_buf.data_ptr(),
-                     ctrl.data_ptr(), s)
-            pend = dict(tag=tag2, cap=cap2, table=table, arena=arena, ctrl=ctrl, ent=ent, counts=counts_buf)
-            ctrl_host = ctrl.cpu().tolist()
+            pend = pend["merged"]  # every rank's admitted entries, re-counted into one table by _exchange
+            ctrl_host = pend["ctrl"].cpu().tolist()
             if int(ctrl_host[2]):
                 raise nat.NativeError(f"merged vocabulary table/arena for {spec.in_key!r} overflowed")
             kept = int(ctrl_host[3])
