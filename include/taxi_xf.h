@@ -60,6 +60,23 @@ TXF_API size_t txf_moments_workspace_bytes(int ncols);
 /* accumulate one chunk into state_dev[ncols*3] (zero-initialised by the caller) */
 TXF_API int txf_moments_update(const void* const* values, const uint8_t* const* valid, const int32_t* dtype,
                        int ncols, int64_t n, double* state_dev, void* workspace_dev, txf_stream_t stream);
+/* Same accumulation, for callers that cannot hand over a workspace.  (No counterpart in the
+ * reference: this entry point exists for the hosts described here.)  Some hosts embed this library
+ * as a plug-in of a larger runtime -- a Beam/TFX worker, a serving process with a fixed device-memory
+ * budget -- which passes input and output buffers in but gives the plug-in no device allocator, and
+ * where a cudaMalloc would stall every stream of the process and take memory outside that budget.
+ * For them the per-block partials live in a fixed array inside the library instead of
+ * workspace_dev: nothing is allocated or freed by this call, ever.
+ *  - limit: at most TXF_NOALLOC_MAX_COLS columns per call (more -> TXF_ERR_ARG with a message);
+ *    the array (about 111 KB) is held by every GPU that loads the library until the process exits;
+ *  - the first call on a device looks up the array's device address; make that first call
+ *    before any stream capture begins on that device;
+ *  - all calls on a device share the array (it keeps whatever the last call left there; each
+ *    call overwrites every partial it later reads, so no clearing is needed): two calls whose
+ *    kernels may overlap on the GPU -- different streams, no ordering between them -- race. */
+#define TXF_NOALLOC_MAX_COLS 4
+TXF_API int txf_moments_update_noalloc(const void* const* values, const uint8_t* const* valid, const int32_t* dtype,
+                               int ncols, int64_t n, double* state_dev, txf_stream_t stream);
 /* Chan-merge nstates states laid out [nstates][ncols][3] in index order (rank order) */
 TXF_API int txf_moments_merge(const double* states_dev, int nstates, int ncols, double* state_out_dev,
                       txf_stream_t stream);

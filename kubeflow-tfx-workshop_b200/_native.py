@@ -50,6 +50,7 @@ _SIGNATURES = {
     "txf_launch_count": (c_int64, []),
     "txf_moments_workspace_bytes": (c_size_t, [c_int]),
     "txf_moments_update": (c_int, [_PP, _PP, POINTER(c_int32), c_int, c_int64, c_void_p, c_void_p, c_void_p]),
+    "txf_moments_update_noalloc": (c_int, [_PP, _PP, POINTER(c_int32), c_int, c_int64, c_void_p, c_void_p]),
     "txf_moments_merge": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p]),
     "txf_moments_finalize": (c_int, [c_void_p, c_int, c_void_p, c_void_p]),
     "txf_msel_state_bytes": (c_size_t, [c_int, c_int]),

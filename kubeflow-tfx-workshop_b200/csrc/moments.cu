@@ -6,6 +6,8 @@
 // through shared memory, blocks through a workspace that a single-CTA kernel folds -- in fixed
 // index order, so the result is bit-reproducible for a given (n, grid).
 // Algorithmic bytes: 4 (f32) or 8 (i64) per row per column + 1 validity bit.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace txf {
@@ -152,6 +154,32 @@ __global__ void moments_finalize_kernel(const double* __restrict__ state, int nc
   mv[2 * c + 1] = static_cast<float>(n > 0.0 ? state[3 * c + 2] / n : 0.0);
 }
 
+// ---- scratch for txf_moments_update_noalloc -------------------------------------------------
+// Block partials of up to TXF_NOALLOC_MAX_COLS columns live in this file-scope device array
+// instead of a caller-provided workspace (~111 KB, held by every GPU that loads the library until
+// the process exits).  In host code the symbol is only a stand-in: its device address has to be
+// asked for, once per device and with that device current.
+static __device__ __align__(256) double g_noalloc_partials[TXF_NOALLOC_MAX_COLS * kMomBlocksPerCol * 3];
+
+constexpr int kMaxDevices = 64;
+static std::mutex g_noalloc_mutex;
+static double* g_noalloc_ptr[kMaxDevices] = {};  // device address of g_noalloc_partials, per device
+
+// Device address of the scratch array on the CURRENT device (looked up on first use).
+static int noalloc_scratch(double** out) {
+  int dev = -1;
+  TXF_CUDA(cudaGetDevice(&dev));
+  TXF_REQUIRE(dev >= 0 && dev < kMaxDevices, "moments_update_noalloc: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+  if (g_noalloc_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    TXF_CUDA(cudaGetSymbolAddress(&p, g_noalloc_partials));
+    g_noalloc_ptr[dev] = static_cast<double*>(p);
+  }
+  *out = g_noalloc_ptr[dev];
+  return TXF_OK;
+}
+
 static int moments_grid(int64_t n, int ncols) {
   int64_t quads = (n >> 2) + 1;
   int64_t want = (quads + kMomBlock - 1) / kMomBlock;
@@ -188,6 +216,37 @@ int txf_moments_update(const void* const* values, const uint8_t* const* valid, c
   moments_partial_kernel<<<dim3(gx, ncols), kMomBlock, 0, s>>>(v, n, static_cast<double*>(workspace_dev));
   TXF_LAUNCH_CHECK();
   moments_fold_kernel<<<ncols, 32, 0, s>>>(static_cast<const double*>(workspace_dev), gx, ncols, state_dev);
+  TXF_LAUNCH_CHECK();
+  count_launch(2);
+  return TXF_OK;
+}
+
+int txf_moments_update_noalloc(const void* const* values, const uint8_t* const* valid, const int32_t* dtype, int ncols,
+                               int64_t n, double* state_dev, txf_stream_t stream) {
+  using namespace txf;
+  TXF_REQUIRE(ncols >= 1 && ncols <= TXF_NOALLOC_MAX_COLS,
+              "moments_update_noalloc: ncols=%d exceeds the built-in scratch (at most %d columns per call; "
+              "use txf_moments_update with a caller workspace for more)", ncols, TXF_NOALLOC_MAX_COLS);
+  TXF_REQUIRE(n >= 0 && n < (1LL << 31), "moments_update_noalloc: n out of range");
+  TXF_REQUIRE(state_dev && values && dtype, "moments_update_noalloc: null pointer");
+  if (n == 0) return TXF_OK;
+  NumColsView v{};
+  for (int c = 0; c < ncols; ++c) {
+    TXF_REQUIRE(values[c] && aligned(values[c], 16), "moments_update_noalloc: column %d values null or not 16B aligned", c);
+    TXF_REQUIRE(dtype[c] == TXF_F32 || dtype[c] == TXF_I64, "moments_update_noalloc: column %d bad dtype", c);
+    v.values[c] = values[c];
+    v.valid[c] = valid ? valid[c] : nullptr;
+    v.dtype[c] = dtype[c];
+  }
+  double* scratch = nullptr;
+  int rc = noalloc_scratch(&scratch);
+  if (rc) return rc;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  int gx = moments_grid(n, ncols);
+  // every partial the fold reads is written by the launch before it, so nothing needs clearing
+  moments_partial_kernel<<<dim3(gx, ncols), kMomBlock, 0, s>>>(v, n, scratch);
+  TXF_LAUNCH_CHECK();
+  moments_fold_kernel<<<ncols, 32, 0, s>>>(scratch, gx, ncols, state_dev);
   TXF_LAUNCH_CHECK();
   count_launch(2);
   return TXF_OK;
