@@ -100,7 +100,7 @@ def _vocab_key(s: VocabSpec) -> Tuple:
 
 class Engine:
     def __init__(self, plan: Plan, device: Union[str, torch.device] = "cuda", comm: Optional[Comm] = None,
-                 vocab_capacity: int = 1 << 16, arena_bytes: int = 1 << 22, sample_size: int = 1 << 21,
+                 vocab_capacity: int = 1 << 16, arena_bytes: int = 1 << 22, sample_size: int = 1 << 20,
                  bracket_sigmas: float = 5.0, seed: int = 20190501):
         self.plan = plan
         self.device = torch.device(device)
@@ -115,6 +115,8 @@ class Engine:
         self._ws: Dict[Tuple, torch.Tensor] = {}
         self.force_general_quantiles = False
         self.use_codes = True   # analyze writes dictionary codes; transform of the same table decodes them
+        self.overlap_streams = True
+        self._side = None
         self.last_quantile_path: Dict[int, str] = {}
 
         self.moment_keys: List[str] = []
@@ -183,11 +185,30 @@ class Engine:
         n_total = sum(n_locals)
         state = TransformState(plan=self.plan, moment_keys=list(self.moment_keys), mean_var=None, moments=None, num_rows=n_total)
 
-        self._analyze_moments(chunks, state)
-        pending_q = {nb: self._quantiles_launch(nb, keys, chunks, n_locals) for nb, keys in self.bucket_groups.items()}
-        pending_v = {vk: self._vocab_count(vk, spec, chunks) for vk, spec in self.vocab_specs.items()}
+        # the three analyzer families are independent: queue them on three streams so that the
+        # HBM-bound moments pass and the issue-bound counting passes share the SMs
+        main = torch.cuda.current_stream()
+        if self.overlap_streams:
+            if self._side is None:
+                self._side = (torch.cuda.Stream(device=self.device), torch.cuda.Stream(device=self.device))
+            sq, sv = self._side
+            start = torch.cuda.Event()
+            start.record(main)
+            sv.wait_event(start)
+            sq.wait_event(start)
+            with torch.cuda.stream(sv):
+                pending_v = {vk: self._vocab_count(vk, spec, chunks) for vk, spec in self.vocab_specs.items()}
+            with torch.cuda.stream(sq):
+                pending_q = {nb: self._quantiles_launch(nb, keys, chunks, n_locals) for nb, keys in self.bucket_groups.items()}
+            self._analyze_moments(chunks, state)
+            main.wait_stream(sv)
+            main.wait_stream(sq)
+        else:
+            self._analyze_moments(chunks, state)
+            pending_q = {nb: self._quantiles_launch(nb, keys, chunks, n_locals) for nb, keys in self.bucket_groups.items()}
+            pending_v = {vk: self._vocab_count(vk, spec, chunks) for vk, spec in self.vocab_specs.items()}
         # one host round trip: everything queued above has to finish before sizes/flags are read
-        torch.cuda.current_stream().synchronize()
+        main.synchronize()
         if self.comm.active:
             self._exchange(pending_q, pending_v)
         for nb, pend in pending_q.items():
