@@ -258,6 +258,11 @@ def run_b200(args):
     else:
         peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
     xf_gbs = (read_b + write_b) / (transform_ms * 1e-3) / 1e9
+    traffic = None  # dram__bytes_read.sum + dram__bytes_write.sum of one transform launch (ncu --set full capture)
+    tpath = os.path.join(ROOT, "profiles", "r1_transform_traffic.json")
+    if os.path.exists(tpath):
+        tj = json.load(open(tpath))
+        traffic = (tj["dram_bytes_read"] + tj["dram_bytes_write"]) * (R / tj["rows"])
     analyze_keys = eng.moment_keys + [k for ks in eng.bucket_groups.values() for k in ks] + [s.in_key for s in eng.vocab_specs.values()]
     analyze_b = table_bytes(table, analyze_keys)
     whole_gbs = (analyze_b + read_b + write_b) / (ms_per_step * 1e-3) / 1e9
@@ -274,7 +279,8 @@ def run_b200(args):
                    "quantile_path": eng.last_quantile_path.get(10), "parallelism": f"rows sharded over {world} GPU(s)"},
         "phases_ms": {"analyze": analyze_ms, "transform": transform_ms},
         "roofline": {"bound": "hbm", "kernel": "transform_kernel", "achieved": xf_gbs, "peak": peak, "unit": "GB/s",
-                     "frac": xf_gbs / peak, "traffic": None, "peak_source": peak_src,
+                     "frac": xf_gbs / peak, "traffic": traffic, "peak_source": peak_src,
+                     "algorithmic_bytes": read_b + write_b,
                      "algorithmic_bytes_per_row": (read_b + write_b) / R, "launch": {"grid": g.value, "block": b.value, "smem": s.value},
                      "whole_pass": {"achieved": whole_gbs, "frac": whole_gbs / peak,
                                     "algorithmic_bytes_per_row": (analyze_b + read_b + write_b) / R}},
