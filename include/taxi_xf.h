@@ -168,6 +168,16 @@ TXF_API int txf_vocab_export_meta(const void* table_dev, const uint32_t* ent_dev
                           uint64_t* tag_dev, uint64_t* count_dev, int32_t* len_dev, txf_stream_t stream);
 TXF_API int txf_vocab_export_bytes(const void* table_dev, const uint8_t* arena_dev, const uint32_t* ent_dev, int64_t m,
                            const int64_t* out_offsets_dev, uint8_t* out_pool_dev, txf_stream_t stream);
+/* fixed-layout exchange of a vocabulary between ranks without host-side sizes: a section is
+ * u64 words [count | a[K] | b[K] | count[K] | len[K] | K byte slots of S bytes].  export fills this
+ * rank's section from the first ctrl[3] listed entries; insert re-counts the sections of all ranks
+ * (rows of an all-gathered buffer) into one table and sets ctrl[2] bit 2 if any section overflowed
+ * (more than K admitted terms or a term longer than S) -- the caller then uses the sized path. */
+TXF_API int txf_vocab_export_blob(const void* table_dev, const uint8_t* arena_dev, const uint32_t* ent_dev,
+                          const uint64_t* ctrl_dev, int64_t K, int64_t S, uint64_t* section_dev, txf_stream_t stream);
+TXF_API int txf_vocab_insert_blob(const uint64_t* blob_dev, int64_t stride_words, int64_t section_offset_words, int nranks,
+                          int64_t K, int64_t S, void* table_dev, int64_t capacity, uint8_t* arena_dev,
+                          int64_t arena_cap, uint64_t* ctrl_dev, txf_stream_t stream);
 /* add m serialised entries (another rank's export) into a table */
 TXF_API int txf_vocab_insert(const uint64_t* fp_dev, const uint64_t* tag_dev, const uint64_t* count_dev,
                      const int64_t* offsets_dev, const uint8_t* pool_dev, int64_t m, void* table_dev,

@@ -262,6 +262,48 @@ __global__ void vocab_insert_kernel(const uint64_t* __restrict__ fp, const uint6
             arena_cap, ctrl);
 }
 
+// ---- fixed-layout exchange section ("blob") of one vocabulary -------------------------------
+// words: [0] = number of admitted entries (bit 62 set: some term longer than the byte slot);
+// then a[K], b[K], count[K], len[K] and K byte slots of S bytes.  Every rank fills one such section,
+// the sections are all-gathered in one collective, and every rank re-counts all of them into one
+// merged table -- no sizes have to travel through the host.
+__global__ void vocab_export_blob_kernel(const CountSlot* __restrict__ table, const uint8_t* __restrict__ arena,
+                                         const uint32_t* __restrict__ ent, const unsigned long long* __restrict__ ctrl,
+                                         int64_t K, int64_t S, unsigned long long* __restrict__ sec) {
+  const int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+  const unsigned long long kept = ctrl[3];
+  if (i == 0) atomicOr(&sec[0], kept);  // caller zeroes word 0; bit 62 may be OR-ed in concurrently
+  if (i >= K || static_cast<unsigned long long>(i) >= kept) return;
+  const CountSlot s = table[ent[i]];
+  const uint32_t len = static_cast<uint32_t>(s.strref & 0xFFFFFFu);
+  sec[1 + i] = s.a;
+  sec[1 + K + i] = s.b;
+  sec[1 + 2 * K + i] = s.count;
+  sec[1 + 3 * K + i] = len;
+  if (len > S) { atomicOr(&sec[0], 1ULL << 62); return; }
+  uint8_t* dst = reinterpret_cast<uint8_t*>(sec + 1 + 4 * K) + i * S;
+  const uint8_t* src = arena + (s.strref >> 24);
+  for (uint32_t k = 0; k < len; ++k) dst[k] = src[k];
+}
+
+__global__ void vocab_insert_blob_kernel(const unsigned long long* __restrict__ blob, int64_t stride_words, int64_t sec_off,
+                                         int W, int64_t K, int64_t S, CountSlot* table, uint64_t mask, uint8_t* arena,
+                                         int64_t arena_cap, unsigned long long* ctrl) {
+  const int64_t idx = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+  if (idx >= static_cast<int64_t>(W) * K) return;
+  const int r = static_cast<int>(idx / K);
+  const int64_t i = idx % K;
+  const unsigned long long* sec = blob + r * stride_words + sec_off;
+  const unsigned long long head = sec[0];
+  const unsigned long long kept = head & ((1ULL << 62) - 1);
+  if (i == 0 && (kept > static_cast<unsigned long long>(K) || (head >> 62))) atomicOr(&ctrl[2], 4ULL);  // section overflowed
+  if (static_cast<unsigned long long>(i) >= kept) return;
+  const uint32_t len = static_cast<uint32_t>(sec[1 + 3 * K + i]);
+  if (len > S) return;
+  table_add(table, mask, sec[1 + i], sec[1 + K + i], sec[1 + 2 * K + i],
+            reinterpret_cast<const uint8_t*>(sec + 1 + 4 * K) + i * S, len, arena, arena_cap, ctrl);
+}
+
 // warp-aggregated append: returns this lane's position in the list counted by *counter
 __device__ __forceinline__ unsigned long long warp_append(bool pred, unsigned long long* counter) {
   unsigned m = __ballot_sync(0xffffffffu, pred);
@@ -502,6 +544,37 @@ int txf_vocab_final_codes(const void* table_dev, int64_t capacity, const uint8_t
       static_cast<const CountSlot*>(table_dev), capacity, arena_dev, local2global_dev, static_cast<const LookupSlot*>(lookup_dev),
       static_cast<uint64_t>(lookup_cap - 1), vocab_size, num_oov_buckets, default_value,
       reinterpret_cast<long long*>(final_code_dev));
+  TXF_LAUNCH_CHECK();
+  count_launch(1);
+  return TXF_OK;
+}
+
+int txf_vocab_export_blob(const void* table_dev, const uint8_t* arena_dev, const uint32_t* ent_dev, const uint64_t* ctrl_dev,
+                          int64_t K, int64_t S, uint64_t* section_dev, txf_stream_t stream) {
+  using namespace txf;
+  TXF_REQUIRE(K >= 1 && S >= 8 && (S & 7) == 0, "vocab_export_blob: need K >= 1 and a byte slot that is a multiple of 8");
+  TXF_REQUIRE(table_dev && arena_dev && ent_dev && ctrl_dev && section_dev, "vocab_export_blob: null pointer");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  TXF_CUDA(cudaMemsetAsync(section_dev, 0, sizeof(uint64_t), s));
+  vocab_export_blob_kernel<<<blocks_for(K, 256), 256, 0, s>>>(static_cast<const CountSlot*>(table_dev), arena_dev, ent_dev,
+                                                              reinterpret_cast<const unsigned long long*>(ctrl_dev), K, S,
+                                                              reinterpret_cast<unsigned long long*>(section_dev));
+  TXF_LAUNCH_CHECK();
+  count_launch(1);
+  return TXF_OK;
+}
+
+int txf_vocab_insert_blob(const uint64_t* blob_dev, int64_t stride_words, int64_t section_offset_words, int nranks, int64_t K,
+                          int64_t S, void* table_dev, int64_t capacity, uint8_t* arena_dev, int64_t arena_cap,
+                          uint64_t* ctrl_dev, txf_stream_t stream) {
+  using namespace txf;
+  TXF_REQUIRE(nranks >= 1 && K >= 1 && S >= 8 && (S & 7) == 0, "vocab_insert_blob: bad sizes");
+  TXF_REQUIRE(pow2(capacity) && capacity < (1LL << 32), "vocab_insert_blob: capacity must be a power of two below 2^32");
+  TXF_REQUIRE(blob_dev && table_dev && arena_dev && ctrl_dev, "vocab_insert_blob: null pointer");
+  vocab_insert_blob_kernel<<<blocks_for(static_cast<int64_t>(nranks) * K, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const unsigned long long*>(blob_dev), stride_words, section_offset_words, nranks, K, S,
+      static_cast<CountSlot*>(table_dev), static_cast<uint64_t>(capacity - 1), arena_dev, arena_cap,
+      reinterpret_cast<unsigned long long*>(ctrl_dev));
   TXF_LAUNCH_CHECK();
   count_launch(1);
   return TXF_OK;

@@ -10,6 +10,8 @@ stream, and there is no CPU fallback (``_native`` raises at import when the libr
 from __future__ import annotations
 
 import math
+import os
+import time
 from dataclasses import dataclass, field
 from typing import Dict, List, Optional, Sequence, Tuple, Union
 
@@ -20,6 +22,7 @@ from .columns import NumericColumn, StringColumn, Table
 from .dist import Comm
 from .plan import BucketSpec, FillSpec, Plan, RatioLabelSpec, VocabSpec, ZScoreSpec
 
+_NO_CAP = 1 << 62  # "no candidate-buffer limit" for txf_qresolve when overflow is tracked elsewhere
 EMPTY_VOCAB_SENTINEL = b"49d0cd50-04bb-48c0-bc6f-5b575dce351a"  # tft's placeholder for an empty vocabulary
 _DT = {"float32": nat.TXF_F32, "int64": nat.TXF_I64}
 
@@ -117,6 +120,12 @@ class Engine:
         self.use_codes = True   # analyze writes dictionary codes; transform of the same table decodes them
         self.overlap_streams = True
         self._side = None
+        # multi-rank merge through ONE all-gather of a fixed-layout buffer (no sizes via the host);
+        # anything that does not fit (more terms / longer terms / more candidates) falls back to the sized exchange
+        self.fixed_exchange = True
+        self.xchg_terms, self.xchg_term_bytes = 4096, 64
+        self.timeline: Dict[str, float] = {}   # TXF_PROFILE=1: wall ms per analyze() segment (with device syncs)
+        self._profile = os.environ.get("TXF_PROFILE") == "1"
         self.last_quantile_path: Dict[int, str] = {}
 
         self.moment_keys: List[str] = []
@@ -152,6 +161,13 @@ class Engine:
             t.zero_()
         return t
 
+    def _tick(self, name: str):
+        if self._profile:
+            torch.cuda.synchronize(self.device)
+            now = time.perf_counter()
+            self.timeline[name] = self.timeline.get(name, 0.0) + (now - self._t0) * 1e3
+            self._t0 = now
+
     @staticmethod
     def _stream() -> int:
         return torch.cuda.current_stream().cuda_stream
@@ -177,12 +193,16 @@ class Engine:
         for c in chunks:
             self._check_table(c)
         n_local = sum(len(c) for c in chunks)
+        if self._profile:
+            torch.cuda.synchronize(self.device)
+            self._t0 = time.perf_counter()
         if self.comm.active:
             nl = torch.tensor([n_local], dtype=torch.int64, device=self.device)
             n_locals = [int(v) for v in self.comm.all_gather(nl).flatten().tolist()]
         else:
             n_locals = [n_local]
         n_total = sum(n_locals)
+        self._tick("row_counts")
         state = TransformState(plan=self.plan, moment_keys=list(self.moment_keys), mean_var=None, moments=None, num_rows=n_total)
 
         # the three analyzer families are independent: queue them on three streams so that the
@@ -209,16 +229,23 @@ class Engine:
             pending_v = {vk: self._vocab_count(vk, spec, chunks) for vk, spec in self.vocab_specs.items()}
         # one host round trip: everything queued above has to finish before sizes/flags are read
         main.synchronize()
+        self._tick("local_pass")
         if self.comm.active:
-            self._exchange(pending_q, pending_v)
+            if self.fixed_exchange:
+                self._exchange_fixed(pending_q, pending_v)
+            else:
+                self._exchange(pending_q, pending_v)
+            self._tick("exchange")
         for nb, pend in pending_q.items():
             state.buckets[nb] = self._quantiles_finish(nb, pend, chunks, n_total)
+        self._tick("quantiles_finish")
         for vk, pend in pending_v.items():
             state.vocabs[vk] = self._vocab_finish(vk, self.vocab_specs[vk], pend)
             for spec in self.plan.of(VocabSpec):  # decode tables depend on num_oov_buckets / default_value
                 if _vocab_key(spec) == vk:
                     self._decode_tables(vk, spec, pend, state.vocabs[vk], state)
                     break
+        self._tick("vocab_finish")
         return state
 
     # -- moments
@@ -344,8 +371,10 @@ class Engine:
             self._quantiles_resolve(nb, pend)
         return pend
 
-    def _quantiles_resolve(self, nb: int, pend):
-        """cells/candidates (already merged across ranks) -> boundaries; all on the stream."""
+    def _quantiles_resolve(self, nb: int, pend, global_count: Optional[torch.Tensor] = None):
+        """cells + candidates -> boundaries; all on the stream.  Multi-rank: `cells` are already
+        summed over ranks and `global_count` holds the total number of candidates per column; the
+        candidates themselves stay where they are -- the selection all-reduces its histograms."""
         keys, T = pend["keys"], pend["T"]
         ncols = len(keys)
         s = self._stream()
@@ -354,25 +383,84 @@ class Engine:
         cand_rank = self._buf(f"q{nb}_cand_rank", (ncols, T), torch.int64)
         status = self._buf(f"q{nb}_status", (ncols,), torch.int32)
         cand, cand_count, cand_cap = pend["cand"], pend["cand_count"], pend["cand_cap"]
-        nat.call("txf_qresolve", pend["cells"].data_ptr(), pend["edges"].data_ptr(), cand_count.data_ptr(), cand_cap,
-                 ranks_dev.data_ptr(), ncols, T, direct.data_ptr(), cand_rank.data_ptr(), status.data_ptr(), s)
+        if global_count is None:
+            nat.call("txf_qresolve", pend["cells"].data_ptr(), pend["edges"].data_ptr(), cand_count.data_ptr(), cand_cap,
+                     ranks_dev.data_ptr(), ncols, T, direct.data_ptr(), cand_rank.data_ptr(), status.data_ptr(), s)
+        else:  # overflow of any rank's buffer is encoded as a count above _NO_CAP
+            nat.call("txf_qresolve", pend["cells"].data_ptr(), pend["edges"].data_ptr(), global_count.data_ptr(), _NO_CAP,
+                     ranks_dev.data_ptr(), ncols, T, direct.data_ptr(), cand_rank.data_ptr(), status.data_ptr(), s)
         cptrs = nat.ptr_array([cand[c].data_ptr() for c in range(ncols)])
 
         def cand_pass(st, p):
             nat.call("txf_msel_hist", st, ncols, T, p, cptrs, None, None, 1, cand.shape[1], cand_count.data_ptr(), s)
 
-        sel = self._msel(f"q{nb}_sel", ncols, T, cand_rank, cand_pass, reduce=False)
+        sel = self._msel(f"q{nb}_sel", ncols, T, cand_rank, cand_pass, reduce=global_count is not None)
         bounds = self._buf(f"q{nb}_bounds", (ncols, T), torch.float32)
         nbound = self._buf(f"q{nb}_nbound", (ncols,), torch.int32)
         nat.call("txf_qfinal", direct.data_ptr(), cand_rank.data_ptr(), sel.data_ptr(), ncols, T, bounds.data_ptr(),
                  nbound.data_ptr(), s)
         pend.update(status=status, bounds=bounds, nbound=nbound)
 
+    @staticmethod
+    def _global_cand_count(counts_all: torch.Tensor, caps_all: torch.Tensor) -> torch.Tensor:
+        """counts_all [W, ncols], caps_all [W, 1] (device) -> per-column total, or _NO_CAP + 1 where some
+        rank overflowed its candidate buffer (txf_qresolve then flags the column)."""
+        over = (counts_all > caps_all).any(dim=0)
+        return torch.where(over, torch.full_like(counts_all[0], _NO_CAP + 1), counts_all.sum(dim=0)).contiguous()
+
+    def _exchange_fixed(self, pending_q, pending_v):
+        """The exchange step as one collective: every rank packs its vocabulary entries, candidate
+        keys and cell counts into a fixed-layout int64 buffer on the device, the buffers are
+        all-gathered, and each rank rebuilds the merged state from all rows -- no size ever goes
+        through the host.  Overflow of a section is flagged on the device and handled later
+        (vocabulary: sized exchange; quantiles: the general radix select)."""
+        dev, W, s = self.device, self.comm.world, self._stream()
+        K, S = self.xchg_terms, self.xchg_term_bytes
+        fast = [(nb, p) for nb, p in pending_q.items() if p["fast"]]
+        voc = list(pending_v.items())
+        off, layout = 0, {}
+        for vk, p in voc:
+            layout[("v", vk)] = off
+            off += 1 + 4 * K + K * S // 8
+        for nb, p in fast:
+            ncols, ncell = len(p["keys"]), 4 * p["T"] + 1
+            layout[("q", nb)] = (off, off + ncols, off + ncols + 1)  # candidate counts, buffer capacity, cells
+            off += ncols + 1 + ncols * ncell
+        if off == 0:
+            return
+        blob = self._buf("xchg_blob", off, torch.int64)
+        for vk, p in voc:
+            o = layout[("v", vk)]
+            nat.call("txf_vocab_export_blob", p["table"].data_ptr(), p["arena"].data_ptr(), p["ent"].data_ptr(), p["ctrl"].data_ptr(),
+                     K, S, blob[o:].data_ptr(), s)
+        for nb, p in fast:
+            ncols = len(p["keys"])
+            oc, ok, ox = layout[("q", nb)]
+            blob[oc:oc + ncols].copy_(p["cand_count"])
+            blob[ok:ox].fill_(p["cand_cap"])
+            blob[ox:ox + p["cells"].numel()].copy_(p["cells"].flatten())
+        g = self.comm.all_gather(blob)  # [W, off] -- the one collective of the exchange
+        for nb, p in fast:
+            ncols = len(p["keys"])
+            oc, ok, ox = layout[("q", nb)]
+            p["cells"].copy_(g[:, ox:ox + p["cells"].numel()].sum(dim=0).view_as(p["cells"]))
+            self._quantiles_resolve(nb, p, self._global_cand_count(g[:, oc:oc + ncols], g[:, ok:ox]))
+        for vk, p in voc:
+            cap2 = max(self.vocab_capacity, _pow2_at_least(2 * W * K))
+            tag2 = p["tag"] + "_merged"
+            table, arena, ctrl, ent, counts_buf = self._vocab_bufs(tag2, cap2)
+            nat.call("txf_vocab_insert_blob", g.data_ptr(), off, layout[("v", vk)], W, K, S, table.data_ptr(), cap2, arena.data_ptr(),
+                     self.arena_bytes, ctrl.data_ptr(), s)
+            nat.call("txf_vocab_compact", table.data_ptr(), cap2, arena.data_ptr(), ent.data_ptr(), counts_buf.data_ptr(),
+                     ctrl.data_ptr(), s)
+            p["merged"] = dict(tag=tag2, cap=cap2, table=table, arena=arena, ctrl=ctrl, ent=ent, counts=counts_buf)
+
     def _exchange(self, pending_q, pending_v):
-        """Merge the per-rank analyzer partials (the one real exchange step of the path) with a
-        handful of collectives: one all-gather of every size, one all-reduce of the cell counts and
-        one padded all-gather of the candidate keys per bucket group, one packed all-gather of the
-        vocabulary entries per vocabulary.  Results land back in the pending dicts."""
+        """Sized variant of the exchange (used when a section of the fixed layout overflows, or with
+        fixed_exchange = False): quantile cell counts are all-reduced and candidate counts
+        all-gathered (the candidate keys never move: the final selection all-reduces its
+        histograms); vocabulary entries travel as one packed all-gather per vocabulary after their
+        sizes went through the host."""
         dev, W = self.device, self.comm.world
         s = self._stream()
         fast = [(nb, p) for nb, p in pending_q.items() if p["fast"]]
@@ -382,32 +470,21 @@ class Engine:
             kept = int(p["ctrl"][3].item())
             p["kept_local"] = kept
             p["export"] = self._export_entries(p, p["ent"], kept)
-        sizes = [p["cand_count"] for _, p in fast]
+        for nb, p in fast:  # quantiles: sum the cells, total the candidate counts; candidates stay local
+            ncols = len(p["keys"])
+            self.comm.all_reduce_sum_(p["cells"])
+            cc = self.comm.all_gather(torch.cat([p["cand_count"], torch.tensor([p["cand_cap"]], dtype=torch.int64, device=dev)]))
+            self._quantiles_resolve(nb, p, self._global_cand_count(cc[:, :ncols], cc[:, ncols:]))
+        sizes = []
         for vk, p in voc:
             sizes.append(torch.tensor([p["kept_local"]], dtype=torch.int64, device=dev))
             sizes.append(p["export"][3][-1:].clone())  # bytes of the exported terms
         if not sizes:
             return
-        all_sizes = self.comm.all_gather(torch.cat(sizes)).cpu()  # [W, K] -- the second (and last but one) host sync
+        self._tick("x_export")
+        all_sizes = self.comm.all_gather(torch.cat(sizes)).cpu()  # [W, K] -- one more host sync
+        self._tick("x_sizes")
         k = 0
-        for nb, p in fast:
-            ncols = len(p["keys"])
-            counts = all_sizes[:, k:k + ncols]
-            k += ncols
-            self.comm.all_reduce_sum_(p["cells"])
-            if int(counts.max()) > p["cand_cap"]:
-                p["fast"] = False  # some rank overflowed its candidate buffer: every rank falls back
-                continue
-            mx = max(int(counts.max()), 1)
-            g = self.comm.all_gather(p["cand"][:, :mx].contiguous())  # [W, ncols, mx]
-            tot = counts.sum(dim=0).tolist()
-            cap = max(max(tot), 1)
-            cand = self._buf(f"q{nb}_cand_merged", (ncols, cap), torch.int32)
-            for c in range(ncols):
-                torch.cat([g[r, c, : int(counts[r, c])] for r in range(W)], out=cand[c, : tot[c]])
-            count = torch.tensor(tot, dtype=torch.int64, device=dev)
-            p.update(cand=cand, cand_count=count, cand_cap=cap)
-            self._quantiles_resolve(nb, p)
         for vk, p in voc:
             kepts = all_sizes[:, k].tolist()
             nbytes = all_sizes[:, k + 1].tolist()
@@ -550,8 +627,11 @@ class Engine:
         self._check_vocab_ctrl(ctrl_host, spec)
         kept = int(ctrl_host[3])
         if self.comm.active:
-            pend = pend["merged"]  # every rank's admitted entries, re-counted into one table by _exchange
-            ctrl_host = pend["ctrl"].cpu().tolist()
+            ctrl_host = pend["merged"]["ctrl"].cpu().tolist()
+            if int(ctrl_host[2]) & 4:  # fixed-layout section overflowed on some rank (same flag everywhere): sized exchange
+                self._exchange({}, {vk: pend})
+                ctrl_host = pend["merged"]["ctrl"].cpu().tolist()
+            pend = pend["merged"]  # every rank's admitted entries, re-counted into one table
             if int(ctrl_host[2]):
                 raise nat.NativeError(f"merged vocabulary table/arena for {spec.in_key!r} overflowed")
             kept = int(ctrl_host[3])

@@ -33,9 +33,13 @@ def main():
     comm = ktw.Comm()
     lo, hi = ktw.shard_range(n, rank, world)
     shard_host = synth.taxi_table(hi - lo, lo, backend="numpy")
-    for force_general in (False, True):
+    # (general quantile engine?, fixed-layout exchange?, tiny exchange sections that force the overflow fallbacks?)
+    for force_general, fixed, tiny in ((False, True, False), (True, True, False), (False, False, False), (False, True, True)):
         eng = ktw.Engine(ktw.trace(fn, synth.TAXI_SCHEMA), device=f"cuda:{local}", comm=comm)
         eng.force_general_quantiles = force_general
+        eng.fixed_exchange = fixed
+        if tiny:
+            eng.xchg_terms = 8
         out, state = eng.analyze_and_transform(shard_host.to(f"cuda:{local}"))
         torch.cuda.synchronize()
         # identical state on every rank
@@ -71,7 +75,8 @@ def main():
             else:
                 assert np.array_equal(col.values.cpu().numpy(), w[lo:hi]), key
         if rank == 0:
-            print(f"multi-gpu parity ok: world={world} rows={n} quantile path={eng.last_quantile_path}", flush=True)
+            print(f"multi-gpu parity ok: world={world} rows={n} fixed_exchange={fixed} tiny={tiny} "
+                  f"quantile path={eng.last_quantile_path}", flush=True)
     dist.barrier()
     dist.destroy_process_group()
 

@@ -17,4 +17,4 @@ def test_two_rank_nccl_parity():
            "--master-port", str(port), os.path.join(ROOT, "tests", "multi_gpu_check.py"), "500001"]
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
     assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
-    assert out.stdout.count("multi-gpu parity ok") == 2
+    assert out.stdout.count("multi-gpu parity ok") == 4
