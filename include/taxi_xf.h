@@ -238,6 +238,48 @@ TXF_API int txf_transform(const txf_op* ops, int nops, int64_t n, txf_stream_t s
 TXF_API int txf_transform_launch_info(int* grid, int* block, int* smem_bytes);
 
 /* ------------------------------------------------------------------------------------------
+ * Sibling analyzers / mappers of the workshop notebooks.
+ *   min/max analyzer + tft.scale_to_0_1 / scale_by_min_max:
+ *     notebooks/03_TensorFlow_Transform.ipynb:148, 03a_TensorFlow_Transform_Advanced.ipynb:323,333
+ *   fp32 arithmetic between columns and analyzer scalars (x - tft.mean(x), a * b):
+ *     notebooks/03_TensorFlow_Transform.ipynb:147,150
+ * min/max state: float[ncols][2] = (min, max) of the FILLED fp32 values (absent cell = 0; int64
+ * cells are converted to fp32 first; NaN cells are skipped).  txf_minmax_begin sets (+inf, -inf);
+ * update folds one chunk into the state; merge folds `nstates` states laid out [state][col][2].
+ * ------------------------------------------------------------------------------------------ */
+TXF_API size_t txf_minmax_workspace_bytes(int ncols);
+TXF_API int txf_minmax_begin(float* state_dev, int ncols, txf_stream_t stream);
+TXF_API int txf_minmax_update(const void* const* values, const uint8_t* const* valid, const int32_t* dtype, int ncols,
+                              int64_t n, float* state_dev, void* workspace_dev, txf_stream_t stream);
+TXF_API int txf_minmax_merge(const float* states_dev, int nstates, int ncols, float* state_out_dev, txf_stream_t stream);
+
+/* One operand of an elementwise fp32 op: a column (fp32 or int64, fill-missing applied, int64
+ * converted to fp32) when col != NULL, else the device scalar *scalar. */
+typedef struct txf_operand {
+  const void* col;
+  const void* valid;
+  const float* scalar;
+  int32_t dtype; /* TXF_F32 | TXF_I64 (columns only) */
+  int32_t reserved;
+} txf_operand;
+enum { TXF_ARITH_ADD = 0, TXF_ARITH_SUB = 1, TXF_ARITH_MUL = 2, TXF_ARITH_DIV = 3 };
+/* out[i] = a[i] (op) b[i]: one correctly rounded fp32 operation per row. */
+TXF_API int txf_map_binary(int opcode, const txf_operand* a, const txf_operand* b, float* out_dev, int64_t n,
+                           txf_stream_t stream);
+/* tf.to_int64 / tf.to_float of a filled column (kubeflow-pipelines/taxi/preprocessing.py:92):
+ * to_dtype TXF_I64 truncates toward zero, TXF_F32 rounds to nearest even. */
+TXF_API int txf_map_cast(const txf_operand* x, int to_dtype, void* out_dev, int64_t n, txf_stream_t stream);
+/* tf.as_string on an int64 feature (kubeflow-pipelines/taxi/preprocessing.py:82), two steps so the
+ * caller owns the prefix sum: lengths (absent cell = "0"), then digits at offsets[i]..offsets[i+1]. */
+TXF_API int txf_i64_format_lengths(const int64_t* values_dev, const uint8_t* valid_dev, int64_t n,
+                                   int32_t* len_out_dev, txf_stream_t stream);
+TXF_API int txf_i64_format_write(const int64_t* values_dev, const uint8_t* valid_dev, int64_t n,
+                                 const int32_t* offsets_dev, uint8_t* pool_out_dev, txf_stream_t stream);
+/* out[i] = (min < max ? (x[i] - min) / (max - min) : 0.5) * (out_max - out_min) + out_min. */
+TXF_API int txf_map_scale_minmax(const txf_operand* x, const float* minmax_dev, float out_min, float out_max,
+                                 float* out_dev, int64_t n, txf_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
  * Test hook: Fingerprint64 of every string of a column (TF StringToHashBucketFast's hash).
  * ------------------------------------------------------------------------------------------ */
 TXF_API int txf_fingerprint64_batch(const int32_t* offsets_dev, const uint8_t* pool_dev, int64_t n, uint64_t* out_dev,

@@ -27,18 +27,19 @@ from .columns import NumericColumn, StringColumn, Table
 from .dist import Comm, shard_range
 from .engine import Engine, TransformState
 from .plan import Plan, trace
-from .state import load_state, save_state
+from .state import TFTransformOutput, load_state, save_state
 
 tf = tf_shim
 tft = tft_shim
 
 __all__ = ["Table", "NumericColumn", "StringColumn", "Engine", "TransformState", "Plan", "trace", "Comm", "shard_range",
-           "tf", "tft", "tft_beam", "tf_metadata", "save_state", "load_state", "install_shims"]
+           "tf", "tft", "tft_beam", "tf_metadata", "save_state", "load_state", "TFTransformOutput", "install_shims"]
 
 _SHIM_MODULES = {
     "tensorflow": tf_shim,
     "tensorflow_transform": tft_shim,
     "tensorflow_transform.beam": tft_beam,
+    "tensorflow_transform.beam.impl": tft_beam,
     "tensorflow_transform.tf_metadata": tf_metadata,
     "tensorflow_transform.tf_metadata.dataset_metadata": tf_metadata.dataset_metadata,
     "tensorflow_transform.tf_metadata.dataset_schema": tf_metadata.dataset_schema,
@@ -53,6 +54,7 @@ def install_shims():
     ``import tensorflow_model_analysis as tfma``, lines 26-29) imports and runs unmodified."""
     tft_shim.beam = tft_beam
     tft_shim.tf_metadata = tf_metadata
+    tft_shim.TFTransformOutput = TFTransformOutput
     mods = dict(_SHIM_MODULES)
     mods["tensorflow_model_analysis"] = types.ModuleType("tensorflow_model_analysis")  # imported, unused on this path
     saved = {k: sys.modules.get(k) for k in mods}

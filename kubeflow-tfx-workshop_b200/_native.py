@@ -36,6 +36,14 @@ class TxfOp(Structure):
     ]
 
 
+class TxfOperand(Structure):
+    """struct txf_operand (include/taxi_xf.h)."""
+
+    _fields_ = [("col", c_void_p), ("valid", c_void_p), ("scalar", c_void_p), ("dtype", c_int32), ("reserved", c_int32)]
+
+
+ARITH_ADD, ARITH_SUB, ARITH_MUL, ARITH_DIV = range(4)
+
 if not os.path.exists(LIB_PATH):
     raise ImportError(
         f"{LIB_PATH} is missing: build it with `python __graft_entry__.py` (or "
@@ -81,6 +89,15 @@ _SIGNATURES = {
     "txf_vocab_lookup_from_terms": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p]),
     "txf_transform": (c_int, [POINTER(TxfOp), c_int, c_int64, c_void_p]),
     "txf_transform_launch_info": (c_int, [POINTER(c_int), POINTER(c_int), POINTER(c_int)]),
+    "txf_minmax_workspace_bytes": (c_size_t, [c_int]),
+    "txf_minmax_begin": (c_int, [c_void_p, c_int, c_void_p]),
+    "txf_minmax_update": (c_int, [_PP, _PP, POINTER(c_int32), c_int, c_int64, c_void_p, c_void_p, c_void_p]),
+    "txf_minmax_merge": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p]),
+    "txf_map_binary": (c_int, [c_int, POINTER(TxfOperand), POINTER(TxfOperand), c_void_p, c_int64, c_void_p]),
+    "txf_map_cast": (c_int, [POINTER(TxfOperand), c_int, c_void_p, c_int64, c_void_p]),
+    "txf_i64_format_lengths": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
+    "txf_i64_format_write": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p]),
+    "txf_map_scale_minmax": (c_int, [POINTER(TxfOperand), c_void_p, c_float, c_float, c_void_p, c_int64, c_void_p]),
     "txf_fingerprint64_batch": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
 }
 

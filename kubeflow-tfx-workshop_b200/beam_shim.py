@@ -66,6 +66,11 @@ def _schema_of(dataset, metadata):
     return dict(metadata)
 
 
+def _dense_of(metadata):
+    sch = metadata.schema if isinstance(metadata, DatasetMetadata) else metadata
+    return set(getattr(sch, "dense_keys", ()))
+
+
 class TransformFn:
     """What AnalyzeDataset returns: the traced plan plus the analyzer state (tft's transform_fn)."""
 
@@ -92,7 +97,7 @@ class AnalyzeDataset(_PTransform):
 
     def _engine(self, dataset, metadata) -> Engine:
         ctx = _context()
-        plan = trace(self.preprocessing_fn, _schema_of(dataset, metadata))
+        plan = trace(self.preprocessing_fn, _schema_of(dataset, metadata), _dense_of(metadata))
         return Engine(plan, device=ctx.device, comm=ctx.comm, **ctx.engine_kwargs)
 
     def expand(self, dataset_and_metadata) -> TransformFn:

@@ -20,7 +20,8 @@ import torch
 from . import _native as nat
 from .columns import NumericColumn, StringColumn, Table
 from .dist import Comm
-from .plan import BucketSpec, FillSpec, Plan, RatioLabelSpec, VocabSpec, ZScoreSpec
+from .plan import (ArithSpec, BucketSpec, CastSpec, FillSpec, Plan, RatioLabelSpec, ScaleSpec, StaticVocabSpec, TEMP_PREFIX,
+                   VocabOnlySpec, VocabSpec, ZScoreSpec)
 
 _NO_CAP = 1 << 62  # "no candidate-buffer limit" for txf_qresolve when overflow is tracked elsewhere
 EMPTY_VOCAB_SENTINEL = b"49d0cd50-04bb-48c0-bc6f-5b575dce351a"  # tft's placeholder for an empty vocabulary
@@ -80,9 +81,20 @@ class TransformState:
     # dictionary codes of the analyzed chunks: (vocab key, id(table)) -> (codes int32[n], decode int64[...]).
     # They alias Engine workspaces and only serve Engine.transform on the very tables that were analyzed.
     codes: Dict[Tuple, Tuple[torch.Tensor, torch.Tensor]] = field(default_factory=dict)
+    minmax_keys: List[str] = field(default_factory=list)
+    minmax: Optional[torch.Tensor] = None                # float32 [n, 2] (min, max) (device)
 
     def mean_var_of(self, key: str):
         return tuple(self.mean_var[self.moment_keys.index(key)].cpu().tolist())
+
+    def min_max_of(self, key: str):
+        return tuple(self.minmax[self.minmax_keys.index(key)].cpu().tolist())
+
+    def scalar(self, kind: str, key: str) -> torch.Tensor:
+        """One-element device view of an analyzer scalar (tft.mean / var / min / max of a feature)."""
+        if kind in ("mean", "var"):
+            return self.mean_var[self.moment_keys.index(key), 0 if kind == "mean" else 1:][:1]
+        return self.minmax[self.minmax_keys.index(key), 0 if kind == "min" else 1:][:1]
 
     def detach(self) -> "TransformState":
         """Copy the state out of the Engine's reusable workspaces.  A state returned by
@@ -94,11 +106,16 @@ class TransformState:
                     for k, v in self.vocabs.items()},
             buckets={k: BucketResult(list(b.keys), b.num_buckets, b.boundaries.clone(), b.nbound.clone(), b.path)
                      for k, b in self.buckets.items()},
-            num_rows=self.num_rows)
+            num_rows=self.num_rows, minmax_keys=list(self.minmax_keys), minmax=c(self.minmax))
 
 
-def _vocab_key(s: VocabSpec) -> Tuple:
-    return (s.in_key, s.top_k, s.frequency_threshold)
+AS_STRING_SUFFIX = "@as_string"  # vocabulary over tf.as_string(int64 feature)
+
+
+def _vocab_key(s) -> Tuple:
+    """(source, top_k, frequency_threshold) of a VocabSpec / VocabOnlySpec: specs with the same key share one analyzer."""
+    src = s.in_key + AS_STRING_SUFFIX if getattr(s, "as_string", False) else s.in_key
+    return (src, s.top_k, s.frequency_threshold)
 
 
 class Engine:
@@ -129,14 +146,21 @@ class Engine:
         self.last_quantile_path: Dict[int, str] = {}
 
         self.moment_keys: List[str] = []
-        for s in plan.of(ZScoreSpec):
-            if s.in_key not in self.moment_keys:
-                self.moment_keys.append(s.in_key)
+        for k in [s.in_key for s in plan.of(ZScoreSpec)] + plan.scalar_keys(("mean", "var")):
+            if k not in self.moment_keys:
+                self.moment_keys.append(k)
+        self.minmax_keys: List[str] = []
+        for k in [s.in_key for s in plan.of(ScaleSpec)] + plan.scalar_keys(("min", "max")):
+            if k not in self.minmax_keys:
+                self.minmax_keys.append(k)
         self.vocab_specs: Dict[Tuple, VocabSpec] = {}
-        for s in plan.of(VocabSpec):
+        for s in plan.of(VocabSpec) + plan.of(VocabOnlySpec):
             if s.frequency_threshold is not None:
                 raise NotImplementedError("frequency_threshold is not supported yet")
             self.vocab_specs.setdefault(_vocab_key(s), s)
+        self._static_vocabs: Dict[str, VocabResult] = {}   # StaticVocabSpec.out_key -> lookup built from its terms
+        self._formatted: Dict[Tuple, Tuple[Table, StringColumn]] = {}  # (id(table), feature) -> tf.as_string column
+        self._consts: Dict[float, torch.Tensor] = {}
         self.bucket_groups: Dict[int, List[str]] = {}
         for s in plan.of(BucketSpec):
             keys = self.bucket_groups.setdefault(s.num_buckets, [])
@@ -147,6 +171,8 @@ class Engine:
                 raise NotImplementedError(f"at most {nat.TXF_MAX_COLS} bucketized features per num_buckets value")
         if len(self.moment_keys) > nat.TXF_MAX_COLS:
             raise NotImplementedError(f"at most {nat.TXF_MAX_COLS} z-scored features")
+        if len(self.minmax_keys) > nat.TXF_MAX_COLS:
+            raise NotImplementedError(f"at most {nat.TXF_MAX_COLS} min/max-scaled features")
 
     # ---- buffers ------------------------------------------------------------------------------
     def _buf(self, name: str, shape, dtype, zero: bool = False) -> torch.Tensor:
@@ -204,6 +230,7 @@ class Engine:
         n_total = sum(n_locals)
         self._tick("row_counts")
         state = TransformState(plan=self.plan, moment_keys=list(self.moment_keys), mean_var=None, moments=None, num_rows=n_total)
+        self._formatted.clear()
 
         # the three analyzer families are independent: queue them on three streams so that the
         # HBM-bound moments pass and the issue-bound counting passes share the SMs
@@ -221,10 +248,12 @@ class Engine:
             with torch.cuda.stream(sq):
                 pending_q = {nb: self._quantiles_launch(nb, keys, chunks, n_locals) for nb, keys in self.bucket_groups.items()}
             self._analyze_moments(chunks, state)
+            self._analyze_minmax(chunks, state)
             main.wait_stream(sv)
             main.wait_stream(sq)
         else:
             self._analyze_moments(chunks, state)
+            self._analyze_minmax(chunks, state)
             pending_q = {nb: self._quantiles_launch(nb, keys, chunks, n_locals) for nb, keys in self.bucket_groups.items()}
             pending_v = {vk: self._vocab_count(vk, spec, chunks) for vk, spec in self.vocab_specs.items()}
         # one host round trip: everything queued above has to finish before sizes/flags are read
@@ -267,6 +296,54 @@ class Engine:
         mv = self._buf("mean_var", (nm, 2), torch.float32)
         nat.call("txf_moments_finalize", mstate.data_ptr(), nm, mv.data_ptr(), s)
         state.moments, state.mean_var = mstate, mv
+
+    # -- min/max (tft.scale_to_0_1 / scale_by_min_max, tft.min / tft.max)
+    def _analyze_minmax(self, chunks, state: TransformState):
+        nm = len(self.minmax_keys)
+        if nm == 0:
+            return
+        s = self._stream()
+        mm = self._buf("minmax_state", (nm, 2), torch.float32)
+        ws = self._buf("minmax_ws", nat.query("txf_minmax_workspace_bytes", nm), torch.uint8)
+        nat.call("txf_minmax_begin", mm.data_ptr(), nm, s)
+        for ch in chunks:
+            if len(ch) == 0:
+                continue
+            v, m, d = self._num_args([ch[k] for k in self.minmax_keys])
+            nat.call("txf_minmax_update", v, m, d, nm, len(ch), mm.data_ptr(), ws.data_ptr(), s)
+        if self.comm.active:
+            gathered = self.comm.all_gather(mm)  # [W, nm, 2]
+            nat.call("txf_minmax_begin", mm.data_ptr(), nm, s)
+            nat.call("txf_minmax_merge", gathered.data_ptr(), self.comm.world, nm, mm.data_ptr(), s)
+        state.minmax_keys, state.minmax = list(self.minmax_keys), mm
+
+    # -- tf.as_string(int64 feature): the decimal text of every cell as a string column
+    def _vocab_source(self, table: Table, spec) -> StringColumn:
+        if not getattr(spec, "as_string", False):
+            return table[spec.in_key]
+        hit = self._formatted.get((id(table), spec.in_key))
+        if hit is not None and hit[0] is table:
+            return hit[1]
+        col: NumericColumn = table[spec.in_key]
+        n, s = len(table), self._stream()
+        offsets = torch.zeros(n + 1, dtype=torch.int32, device=self.device)
+        total = 0
+        if n:
+            lens = torch.empty(n, dtype=torch.int32, device=self.device)
+            nat.call("txf_i64_format_lengths", col.values.data_ptr(), _ptr(col.valid), n, lens.data_ptr(), s)
+            ends = torch.cumsum(lens, 0, dtype=torch.int64)
+            total = int(ends[-1].item())
+            if total >= 1 << 31:
+                raise nat.NativeError(f"tf.as_string({spec.in_key!r}): more than 2 GiB of text in one chunk; split the table")
+            offsets[1:] = ends.to(torch.int32)
+        pool = torch.zeros(total + nat.TXF_POOL_SLACK, dtype=torch.uint8, device=self.device)
+        if n:
+            nat.call("txf_i64_format_write", col.values.data_ptr(), _ptr(col.valid), n, offsets.data_ptr(), pool.data_ptr(), s)
+        out = StringColumn(offsets, pool, None, total)
+        if len(self._formatted) >= 16:
+            self._formatted.clear()
+        self._formatted[(id(table), spec.in_key)] = (table, out)
+        return out
 
     # -- exact multi-rank selection driver (general engine)
     def _msel(self, name: str, ncols: int, R: int, ranks_dev: torch.Tensor, passes_fn, reduce: bool) -> torch.Tensor:
@@ -565,7 +642,7 @@ class Engine:
 
     def _vocab_count(self, vk: Tuple, spec: VocabSpec, chunks):
         s = self._stream()
-        tag = f"v_{spec.in_key}_{spec.top_k}"
+        tag = f"v_{vk[0]}_{spec.top_k}"
         cap = self.vocab_capacity
         table, arena, ctrl, ent, counts = self._vocab_bufs(tag, cap)
         coded = []
@@ -573,7 +650,7 @@ class Engine:
         for i, ch in enumerate(chunks):
             if len(ch) == 0:
                 continue
-            col: StringColumn = ch[spec.in_key]
+            col: StringColumn = self._vocab_source(ch, spec)
             codes = self._buf(f"{tag}_codes{i}", len(ch), torch.int32)
             l2g = self._buf(f"{tag}_l2g{i}", nlocal, torch.int32)
             nat.call("txf_vocab_count", col.offsets.data_ptr(), col.pool.data_ptr(), _ptr(col.valid), len(ch), table.data_ptr(),
@@ -672,16 +749,47 @@ class Engine:
         return VocabResult(vk, k, lookup, lookup_cap, col.offsets, col.pool)
 
     # ---- transform ----------------------------------------------------------------------------
+    def _static_vocab(self, spec: StaticVocabSpec) -> VocabResult:
+        res = self._static_vocabs.get(spec.out_key)
+        if res is None:
+            res = self._vocab_from_terms(("static", spec.out_key), [t.encode("latin-1") for t in spec.terms])
+            self._static_vocabs[spec.out_key] = res
+        return res
+
+    def _const(self, value: float) -> torch.Tensor:
+        t = self._consts.get(value)
+        if t is None:
+            t = torch.tensor([value], dtype=torch.float32, device=self.device)
+            self._consts[value] = t
+        return t
+
+    def _operand(self, o: list, table: Table, state: TransformState, made: Dict[str, torch.Tensor]) -> nat.TxfOperand:
+        """txf_operand of one ArithSpec operand (see plan.ArithSpec)."""
+        r = nat.TxfOperand()
+        if o[0] == "col":
+            col = table[o[1]]
+            r.col, r.valid, r.dtype = col.values.data_ptr(), _ptr(col.valid), _DT[col.dtype]
+        elif o[0] == "out":
+            r.col, r.dtype = made[o[1]].data_ptr(), nat.TXF_F32
+        elif o[0] == "scalar":
+            r.scalar = state.scalar(o[1], o[2]).data_ptr()
+        else:
+            r.scalar = self._const(float(o[1])).data_ptr()
+        return r
+
     def transform(self, table: Table, state: TransformState, out: Optional[Table] = None) -> Table:
-        """Launch the fused transform kernel over one GPU-resident chunk; returns the output table
-        (reusing `out`'s buffers when given)."""
+        """One fused kernel for the ops of the taxi program over one GPU-resident chunk, then one
+        small kernel per sibling mapper (scale, arithmetic, cast) in dependency order; returns the
+        output table (reusing `out`'s buffers when given)."""
         self._check_table(table)
         n = len(table)
         dev = self.device
-        ops = (nat.TxfOp * len(self.plan.specs))()
+        fused = [sp for sp in self.plan.specs if isinstance(sp, (ZScoreSpec, BucketSpec, VocabSpec, StaticVocabSpec, FillSpec,
+                                                                   RatioLabelSpec))]
+        ops = (nat.TxfOp * max(len(fused), 1))()
         cols: Dict[str, object] = {}
         copies = []
-        for i, spec in enumerate(self.plan.specs):
+        for i, spec in enumerate(fused):
             op = ops[i]
             prev = out[spec.out_key] if out is not None else None
             if isinstance(spec, RatioLabelSpec):
@@ -708,18 +816,22 @@ class Engine:
                 op.in0, op.valid0 = col.values.data_ptr(), _ptr(col.valid)
                 op.p0, op.p1, op.a0 = res.boundaries[c].data_ptr(), res.nbound[c].data_ptr(), res.boundaries.shape[1]
                 cols[spec.out_key] = NumericColumn(o)
-            elif isinstance(spec, VocabSpec):
-                res = state.vocabs[_vocab_key(spec)]
+            elif isinstance(spec, (VocabSpec, StaticVocabSpec)):
                 o = prev.values if prev is not None else torch.empty(n, dtype=torch.int64, device=dev)
-                coded = state.codes.get((_vocab_key(spec), id(table)))
-                first = next(sp for sp in self.plan.of(VocabSpec) if _vocab_key(sp) == _vocab_key(spec))
-                if (coded is not None and coded[0].numel() == n and self.use_codes
-                        and (first.num_oov_buckets, first.default_value) == (spec.num_oov_buckets, spec.default_value)):
-                    op.kind = nat.OP_VOCAB_CODED  # this very table was analyzed: decode its dictionary codes
-                    op.in0, op.p0 = coded[0].data_ptr(), coded[1].data_ptr()
-                    op.out = o.data_ptr()
-                    cols[spec.out_key] = NumericColumn(o)
-                    continue
+                if isinstance(spec, StaticVocabSpec):
+                    res = self._static_vocab(spec)
+                else:
+                    res = state.vocabs[_vocab_key(spec)]
+                    coded = state.codes.get((_vocab_key(spec), id(table)))
+                    first = next(sp for sp in self.plan.of(VocabSpec) if _vocab_key(sp) == _vocab_key(spec))
+                    if (coded is not None and coded[0].numel() == n and self.use_codes
+                            and (first.num_oov_buckets, first.default_value) == (spec.num_oov_buckets, spec.default_value)):
+                        op.kind = nat.OP_VOCAB_CODED  # this very table was analyzed: decode its dictionary codes
+                        op.in0, op.p0 = coded[0].data_ptr(), coded[1].data_ptr()
+                        op.out = o.data_ptr()
+                        cols[spec.out_key] = NumericColumn(o)
+                        continue
+                    col = self._vocab_source(table, spec)
                 op.kind = nat.OP_VOCAB
                 op.in0, op.valid0, op.pool = col.offsets.data_ptr(), _ptr(col.valid), col.pool.data_ptr()
                 op.p0, op.a0, op.a1, op.a2, op.a3 = res.lookup.data_ptr(), res.lookup_cap, res.size, spec.num_oov_buckets, spec.default_value
@@ -745,12 +857,36 @@ class Engine:
             else:  # pragma: no cover
                 raise AssertionError(spec)
             op.out = o.data_ptr()
-        if n:
-            nat.call("txf_transform", ops, len(self.plan.specs), n, self._stream())
+        if n and fused:
+            nat.call("txf_transform", ops, len(fused), n, self._stream())
             for o_pool, col in copies:  # bytes of pass-through string features: plain device copy
                 if col.pool_bytes:
                     o_pool[: col.pool_bytes].copy_(col.pool[: col.pool_bytes], non_blocking=True)
-        return Table(cols)
+        # sibling mappers: plan order already has every operand before its user
+        made: Dict[str, torch.Tensor] = {k: c.values for k, c in cols.items() if isinstance(c, NumericColumn)}
+        for spec in self.plan.specs:
+            if not isinstance(spec, (ScaleSpec, ArithSpec, CastSpec)):
+                continue
+            prev = out[spec.out_key] if out is not None and spec.out_key in out else None
+            dt = torch.int64 if isinstance(spec, CastSpec) and spec.to == "int64" else torch.float32
+            o = prev.values if prev is not None else torch.empty(n, dtype=dt, device=dev)
+            if n:
+                if isinstance(spec, ScaleSpec):
+                    x = self._operand(["col", spec.in_key], table, state, made)
+                    nat.call("txf_map_scale_minmax", x, state.minmax[state.minmax_keys.index(spec.in_key)].data_ptr(),
+                             spec.output_min, spec.output_max, o.data_ptr(), n, self._stream())
+                elif isinstance(spec, ArithSpec):
+                    code = {"add": nat.ARITH_ADD, "sub": nat.ARITH_SUB, "mul": nat.ARITH_MUL, "div": nat.ARITH_DIV}[spec.op]
+                    nat.call("txf_map_binary", code, self._operand(spec.a, table, state, made),
+                             self._operand(spec.b, table, state, made), o.data_ptr(), n, self._stream())
+                else:
+                    nat.call("txf_map_cast", self._operand(["col", spec.in_key], table, state, made), _DT[spec.to], o.data_ptr(), n,
+                             self._stream())
+            made[spec.out_key] = o
+            if not spec.out_key.startswith(TEMP_PREFIX):
+                cols[spec.out_key] = NumericColumn(o)
+        order = [sp.out_key for sp in self.plan.specs if sp.out_key in cols and not sp.out_key.startswith(TEMP_PREFIX)]
+        return Table({k: cols[k] for k in order})
 
     def analyze_and_transform(self, data: Union[Table, Sequence[Table]]):
         chunks = [data] if isinstance(data, Table) else list(data)

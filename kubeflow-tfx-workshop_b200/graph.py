@@ -45,6 +45,34 @@ class Node:
     def children(self) -> Tuple["Node", ...]:
         return ()
 
+    # tensor arithmetic (`x - tft.mean(x)`, `a * b`: notebooks/03_TensorFlow_Transform.ipynb:147,150)
+    def __add__(self, o):
+        return Arith("add", self, as_node(o))
+
+    def __radd__(self, o):
+        return Arith("add", as_node(o), self)
+
+    def __sub__(self, o):
+        return Arith("sub", self, as_node(o))
+
+    def __rsub__(self, o):
+        return Arith("sub", as_node(o), self)
+
+    def __mul__(self, o):
+        return Arith("mul", self, as_node(o))
+
+    def __rmul__(self, o):
+        return Arith("mul", as_node(o), self)
+
+    def __truediv__(self, o):
+        return Arith("div", self, as_node(o))
+
+    def __rtruediv__(self, o):
+        return Arith("div", as_node(o), self)
+
+    __div__, __rdiv__ = __truediv__, __rtruediv__
+    __hash__ = object.__hash__
+
     def describe(self) -> str:
         kids = ", ".join(c.describe() for c in self.children())
         return f"{type(self).__name__}({kids})"
@@ -202,6 +230,97 @@ class Bucketize(Unary):
         super().__init__(x, int64)
         self.num_buckets = num_buckets
         self.epsilon = epsilon
+
+
+# ---- sibling analyzers / mappers of the workshop notebooks ---------------------
+class Arith(Binary):
+    """One float32 operation between two tensors (either may be a scalar)."""
+
+    def __init__(self, op: str, a: Node, b: Node):
+        super().__init__(a, b, float32)
+        self.op = op
+
+    def describe(self):
+        return f"{self.op}({self.a.describe()}, {self.b.describe()})"
+
+
+class Reduce(Unary):
+    """tft.mean / tft.min / tft.max / tft.var: a full-pass analyzer whose result is a scalar."""
+
+    rank = 0
+
+    def __init__(self, kind: str, x: Node):
+        super().__init__(x, float32)
+        self.kind = kind
+        self.rank = 0
+
+    def describe(self):
+        return f"tft.{self.kind}({self.x.describe()})"
+
+
+class ScaleMinMax(Unary):
+    """tft.scale_by_min_max(x, output_min, output_max) / tft.scale_to_0_1(x)
+    (notebooks/03_TensorFlow_Transform.ipynb:148)."""
+
+    def __init__(self, x, output_min: float, output_max: float):
+        super().__init__(x, float32)
+        self.output_min, self.output_max = float(output_min), float(output_max)
+
+
+class VocabFile(Unary):
+    """tft.vocabulary(x, ..., vocab_filename=): analyzer only; the value is a deferred file name
+    (notebooks/03a_TensorFlow_Transform_Advanced.ipynb:341)."""
+
+    rank = 0
+
+    def __init__(self, x, top_k, frequency_threshold, vocab_filename):
+        super().__init__(x, string)
+        self.top_k, self.frequency_threshold, self.vocab_filename = top_k, frequency_threshold, vocab_filename
+        self.rank = 0
+
+
+class StaticVocab(Unary):
+    """tf.contrib.lookup.index_table_from_tensor(mapping).lookup(x) (03a_...:344-345)."""
+
+    def __init__(self, x, terms, num_oov_buckets, default_value):
+        super().__init__(x, int64)
+        self.terms, self.num_oov_buckets, self.default_value = list(terms), num_oov_buckets, default_value
+
+
+# ---- KFP variant (kubeflow-pipelines/taxi/preprocessing.py:65-101, SURVEY.md 8 f3) ---------------
+class AsString(Unary):
+    """tf.as_string(x) on an integer feature (:82): shortest decimal text."""
+
+    def __init__(self, x):
+        super().__init__(x, string)
+
+
+class LogicalNot(Unary):
+    def __init__(self, x):
+        super().__init__(x, bool_)
+
+
+class LogicalAnd(Binary):
+    def __init__(self, a, b):
+        super().__init__(a, b, bool_)
+
+
+# Analyzers that are requested without being part of an output expression (tft.vocabulary) register
+# themselves with the trace in progress.
+_TRACES = []
+
+
+def begin_trace():
+    _TRACES.append([])
+
+
+def end_trace():
+    return _TRACES.pop()
+
+
+def register_side_analyzer(node):
+    if _TRACES:
+        _TRACES[-1].append(node)
 
 
 def as_node(x) -> Node:

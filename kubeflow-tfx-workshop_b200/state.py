@@ -17,7 +17,8 @@ import torch
 from . import plan as P
 from .engine import BucketResult, Engine, TransformState, _vocab_key
 
-_SPEC_TYPES = {c.__name__: c for c in (P.ZScoreSpec, P.VocabSpec, P.BucketSpec, P.FillSpec, P.RatioLabelSpec)}
+_SPEC_TYPES = {c.__name__: c for c in (P.ZScoreSpec, P.VocabSpec, P.BucketSpec, P.FillSpec, P.RatioLabelSpec, P.VocabOnlySpec,
+                                       P.StaticVocabSpec, P.ScaleSpec, P.ArithSpec, P.CastSpec)}
 
 
 def _vocab_file(key) -> str:
@@ -34,6 +35,7 @@ def save_state(state: TransformState, path: str) -> None:
         "specs": [dict(type=type(s).__name__, **dataclasses.asdict(s)) for s in state.plan.specs],
         "moments": {},
         "buckets": {},
+        "minmax": {},
         "vocabs": [],
     }
     if state.mean_var is not None:
@@ -42,6 +44,14 @@ def save_state(state: TransformState, path: str) -> None:
         for i, k in enumerate(state.moment_keys):
             doc["moments"][k] = {"mean_f32_hex": float(mv[i, 0]).hex(), "var_f32_hex": float(mv[i, 1]).hex(),
                                  "count": float(m[i, 0]), "mean": float(m[i, 1]), "m2": float(m[i, 2])}
+    if state.minmax is not None:
+        mm = state.minmax.cpu().numpy()
+        for i, k in enumerate(state.minmax_keys):
+            doc["minmax"][k] = {"min_f32_hex": float(mm[i, 0]).hex(), "max_f32_hex": float(mm[i, 1]).hex()}
+    named = {}  # vocab key -> file name the user asked for (vocab_filename=)
+    for sp in state.plan.of(P.VocabSpec) + state.plan.of(P.VocabOnlySpec):
+        if sp.vocab_filename:
+            named.setdefault(_vocab_key(sp), sp.vocab_filename)
     for nb, res in state.buckets.items():
         doc["buckets"][str(nb)] = {k: [float(x).hex() for x in res.boundaries_of(k)] for k in res.keys}
     for key, res in state.vocabs.items():
@@ -49,7 +59,11 @@ def save_state(state: TransformState, path: str) -> None:
         with open(os.path.join(path, fname), "wb") as f:
             for t in res.terms():
                 f.write(t + b"\n")
-        doc["vocabs"].append({"key": list(key), "file": fname, "size": res.size})
+        doc["vocabs"].append({"key": list(key), "file": fname, "size": res.size, "vocab_filename": named.get(key)})
+        if key in named:  # tft stores the asset under the name the user gave (vocabulary_file_by_name)
+            with open(os.path.join(path, named[key]), "wb") as f:
+                for t in res.terms():
+                    f.write(t + b"\n")
     with open(os.path.join(path, "state.json"), "w") as f:
         json.dump(doc, f, indent=1)
 
@@ -73,6 +87,11 @@ def load_state(path: str, device="cuda", comm=None):
         moments = torch.tensor([[doc["moments"][k]["count"], doc["moments"][k]["mean"], doc["moments"][k]["m2"]] for k in keys],
                                dtype=torch.float64, device=dev)
     state = TransformState(plan=plan, moment_keys=keys, mean_var=mean_var, moments=moments, num_rows=doc["num_rows"])
+    mk = list(doc.get("minmax", {}).keys())
+    if mk:
+        state.minmax_keys = mk
+        state.minmax = torch.tensor([[float.fromhex(doc["minmax"][k]["min_f32_hex"]), float.fromhex(doc["minmax"][k]["max_f32_hex"])]
+                                     for k in mk], dtype=torch.float32, device=dev)
     for nb_s, cols in doc["buckets"].items():
         nb = int(nb_s)
         ks = list(cols.keys())
@@ -91,3 +110,41 @@ def load_state(path: str, device="cuda", comm=None):
         key = tuple(v["key"])
         state.vocabs[key] = eng._vocab_from_terms(key, terms)
     return eng, state
+
+
+class TFTransformOutput:
+    """``tft.TFTransformOutput(dir)`` (``airflow-dags/taxi_utils.py:307``,
+    ``notebooks/03a_TensorFlow_Transform_Advanced.ipynb``): reads what WriteTransformFn wrote."""
+
+    def __init__(self, transform_output_dir: str, device="cuda", comm=None):
+        self.transform_output_dir = transform_output_dir
+        self._device, self._comm = device, comm
+        self._loaded = None
+        with open(os.path.join(transform_output_dir, "state.json")) as f:
+            self._doc = json.load(f)
+
+    def _load(self):
+        if self._loaded is None:
+            self._loaded = load_state(self.transform_output_dir, self._device, self._comm)
+        return self._loaded
+
+    def transform_raw_features(self, raw_features):
+        """Apply the saved transform to a GPU-resident Table of raw features (:211-212, :244-245)."""
+        eng, state = self._load()
+        return eng.transform(raw_features, state)
+
+    def vocabulary_file_by_name(self, vocab_filename: str) -> str:
+        for v in self._doc["vocabs"]:
+            if v.get("vocab_filename") == vocab_filename:
+                return os.path.join(self.transform_output_dir, vocab_filename)
+        raise KeyError(f"no vocabulary was saved under the name {vocab_filename!r}")
+
+    def vocabulary_size_by_name(self, vocab_filename: str) -> int:
+        for v in self._doc["vocabs"]:
+            if v.get("vocab_filename") == vocab_filename:
+                return int(v["size"])
+        raise KeyError(f"no vocabulary was saved under the name {vocab_filename!r}")
+
+    def transformed_feature_spec(self) -> Dict[str, str]:
+        """Output feature -> 'float32' | 'int64' | 'bytes'."""
+        return self._load()[0].plan.output_schema()

@@ -89,7 +89,63 @@ def where(condition, x=None, y=None, name=None):
     return g.Where(g.as_node(condition), g.as_node(x), g.as_node(y))
 
 
-math = types.SimpleNamespace(is_nan=is_nan, greater=greater, multiply=multiply)
+def add(x, y, name=None):
+    return g.as_node(x) + y
+
+
+def subtract(x, y, name=None):
+    return g.as_node(x) - y
+
+
+def divide(x, y, name=None):
+    return g.as_node(x) / y
+
+
+def to_float(x, name="ToFloat"):
+    return g.Cast(g.as_node(x), g.float32)
+
+
+def to_int64(x, name="ToInt64"):
+    return g.Cast(g.as_node(x), g.int64)
+
+
+def as_string(input, precision=-1, scientific=False, shortest=False, width=-1, fill="", name=None):  # noqa: A002
+    x = g.as_node(input)
+    if x.dtype not in (g.int64, g.int32) or (precision, scientific, shortest, width, fill) != (-1, False, False, -1, ""):
+        raise NotImplementedError("tf.as_string: only integer tensors with default formatting are supported")
+    return g.AsString(x)
+
+
+def logical_not(x, name=None):
+    return g.LogicalNot(g.as_node(x))
+
+
+def logical_and(x, y, name=None):
+    return g.LogicalAnd(g.as_node(x), g.as_node(y))
+
+
+math = types.SimpleNamespace(is_nan=is_nan, greater=greater, multiply=multiply, add=add, subtract=subtract, divide=divide,
+                             logical_and=logical_and, logical_not=logical_not)
+strings = types.SimpleNamespace(as_string=as_string)
+
+
+class _StaticTable:
+    """tf.contrib.lookup.index_table_from_tensor(mapping) (03a_TensorFlow_Transform_Advanced.ipynb:344)."""
+
+    def __init__(self, mapping, num_oov_buckets, default_value):
+        self.mapping, self.num_oov_buckets, self.default_value = list(mapping), num_oov_buckets, default_value
+
+    def lookup(self, keys, name=None):
+        return g.StaticVocab(g.as_node(keys), self.mapping, self.num_oov_buckets, self.default_value)
+
+
+def _index_table_from_tensor(mapping, num_oov_buckets=0, default_value=-1, hasher_spec=None, dtype=string, name=None):
+    return _StaticTable(mapping, num_oov_buckets, default_value)
+
+
+contrib = types.SimpleNamespace(lookup=types.SimpleNamespace(index_table_from_tensor=_index_table_from_tensor))
+lookup = types.SimpleNamespace(index_table_from_tensor=_index_table_from_tensor)
+logging = types.SimpleNamespace(ERROR=40, WARN=30, INFO=20, set_verbosity=lambda level: None)
 
 
 class FixedLenFeature:

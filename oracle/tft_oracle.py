@@ -534,3 +534,68 @@ def transform(cols, state, num_oov_buckets=OOV_SIZE, use_c_hash=True):
 def analyze_and_transform(cols):
     state = analyze(cols)
     return transform(cols, state), state
+
+
+# =================================================================================================
+# Sibling analyzers / mappers of the workshop notebooks.  TEST INFRASTRUCTURE like
+# everything above.  Semantics [UPSTREAM-RECALLED, tft 0.13 mappers.py / analyzers.py]:
+#   tft.mean(x)             -> mean of all values, in x's dtype (float32 here: fp64 sum, one rounding)
+#   tft.scale_to_0_1(x)     == scale_by_min_max(x, 0, 1): where(min < max, (x - min) / (max - min), 0.5),
+#                              then * (output_max - output_min) + output_min; every step in float32
+#   tft.vocabulary(x, ...)  == the analyzer half of compute_and_apply_vocabulary
+# Pinned by the reference: notebooks/03_TensorFlow_Transform.ipynb:227-231 (x=[1,2,3], y=[1,2,3],
+# s=[hello,world,hello] -> [-1,0,1], [0,.5,1], [0,1,0], [-0,0,1]); see notebook03_example().
+# Unpinned: behaviour for NaN input (here: NaN cells never become min or max).
+# =================================================================================================
+def min_max(x_filled):
+    """(min, max) as float32 of the filled values; (+inf, -inf) for an empty column."""
+    x = np.asarray(x_filled).astype(np.float32)
+    x = x[~np.isnan(x)]
+    if x.size == 0:
+        return np.float32(np.inf), np.float32(-np.inf)
+    return np.float32(x.min()), np.float32(x.max())
+
+
+def merge_min_max(a, b):
+    return np.float32(min(a[0], b[0])), np.float32(max(a[1], b[1]))
+
+
+def mean_f32(x_filled):
+    """tft.mean: the same fp64-accumulated mean the z-score uses, rounded once to float32."""
+    return finalize_moments(moments(x_filled))[0]
+
+
+def scale_by_min_max(x_filled, mn, mx, output_min=0.0, output_max=1.0):
+    x = np.asarray(x_filled).astype(np.float32)
+    mn, mx = np.float32(mn), np.float32(mx)
+    omin, omax = np.float32(output_min), np.float32(output_max)
+    with np.errstate(all="ignore"):
+        if mn < mx:
+            r = ((x - mn).astype(np.float32) / np.float32(mx - mn)).astype(np.float32)
+        else:
+            r = np.full(x.shape, 0.5, np.float32)
+        return ((r * np.float32(omax - omin)).astype(np.float32) + omin).astype(np.float32)
+
+
+_ARITH = {"add": np.add, "sub": np.subtract, "mul": np.multiply, "div": np.divide}
+
+
+def arith_f32(op, a, b):
+    """One float32 operation per row; scalars broadcast."""
+    with np.errstate(all="ignore"):
+        return _ARITH[op](np.asarray(a, np.float32), np.asarray(b, np.float32)).astype(np.float32)
+
+
+def notebook03_example(x, y, s):
+    """The preprocessing_fn of notebooks/03_TensorFlow_Transform.ipynb:141-157 on dense columns."""
+    x = np.asarray(x, np.float32)
+    y = np.asarray(y, np.float32)
+    x_centered = arith_f32("sub", x, mean_f32(x))
+    y_normalized = scale_by_min_max(y, *min_max(y))
+    vocab = finalize_vocabulary(vocab_counts(s))
+    return {
+        "x_centered": x_centered,
+        "y_normalized": y_normalized,
+        "s_integerized": apply_vocabulary(s, vocab, num_oov_buckets=0, default_value=-1),
+        "x_centered_times_y_normalized": arith_f32("mul", x_centered, y_normalized),
+    }

@@ -288,3 +288,70 @@ def test_two_rank_exchange_over_gloo(ktw):
         assert hist_tot == [n] * 4 and nk == n and sum(counts) == n
         assert vocab == dict(whole["vocab"]["company"])
     assert results[0][1] == results[1][1]  # identical on every rank (rank-ordered merge)
+
+
+# ------------------------------------------------------------------------------------------------
+# tracing of the sibling shapes (no GPU needed: tracing computes nothing)
+# ------------------------------------------------------------------------------------------------
+def test_oracle_reproduces_notebook03_known_answer():
+    """notebooks/03_TensorFlow_Transform.ipynb:227-231 -- the one result the reference states."""
+    r = O.notebook03_example([1, 2, 3], [1, 2, 3], [b"hello", b"world", b"hello"])
+    assert r["x_centered"].tolist() == [-1.0, 0.0, 1.0]
+    assert r["y_normalized"].tolist() == [0.0, 0.5, 1.0]
+    assert r["s_integerized"].tolist() == [0, 1, 0]
+    assert r["x_centered_times_y_normalized"].tolist() == [0.0, 0.0, 1.0]
+    assert np.signbit(r["x_centered_times_y_normalized"]).tolist() == [True, False, False]
+    assert O.scale_by_min_max(np.array([4, 4], np.float32), 4, 4).tolist() == [0.5, 0.5]
+
+
+def test_trace_notebook03_and_kfp_variants(ktw):
+    tf, tft = ktw.tf, ktw.tft
+
+    def nb03(inputs):
+        x_centered = inputs["x"] - tft.mean(inputs["x"])
+        y_normalized = tft.scale_to_0_1(inputs["y"])
+        return {"x_centered": x_centered, "y_normalized": y_normalized,
+                "s_integerized": tft.compute_and_apply_vocabulary(inputs["s"]),
+                "x_centered_times_y_normalized": x_centered * y_normalized}
+
+    sch = ktw.tf_metadata.dataset_schema.from_feature_spec({
+        "x": tf.FixedLenFeature([], tf.float32), "y": tf.FixedLenFeature([], tf.float32), "s": tf.FixedLenFeature([], tf.string)})
+    assert sch.dense_keys == {"x", "y", "s"}
+    plan = ktw.trace(nb03, sch)
+    kinds = [type(s).__name__ for s in plan.specs]
+    assert kinds == ["ArithSpec", "ScaleSpec", "VocabSpec", "ArithSpec"]
+    assert plan.specs[0].a == ["col", "x"] and plan.specs[0].b == ["scalar", "mean", "x"]
+    assert plan.specs[3].a == ["out", "x_centered"] and plan.specs[3].b == ["out", "y_normalized"]
+    assert plan.output_schema() == {"x_centered": "float32", "y_normalized": "float32", "s_integerized": "int64",
+                                    "x_centered_times_y_normalized": "float32"}
+
+    # an operand that is not itself an output becomes a hidden temporary, emitted before its user
+    plan2 = ktw.trace(lambda i: {"o": (i["x"] - tft.mean(i["x"])) * tft.scale_to_0_1(i["y"])}, sch)
+    assert [s.out_key for s in plan2.specs] == ["__tmp0", "__tmp1", "o"] and list(plan2.output_schema()) == ["o"]
+
+    # tft.vocabulary is an analyzer without an output column
+    plan3 = ktw.trace(lambda i: (tft.vocabulary(i["s"], vocab_filename="s_vocab"), {"s": i["s"]})[1], sch)
+    assert [type(s).__name__ for s in plan3.specs] == ["VocabOnlySpec", "FillSpec"] and list(plan3.output_schema()) == ["s"]
+
+    with pytest.raises(NotImplementedError, match="at least one operand must be a column"):
+        ktw.trace(lambda i: {"o": tft.mean(i["x"]) - 1.0}, sch)
+    with pytest.raises(ValueError, match="output_min"):
+        ktw.trace(lambda i: {"o": tft.scale_by_min_max(i["x"], 1.0, 1.0)}, sch)
+
+    ref = "/root/reference/kubeflow-pipelines/taxi/preprocessing.py"
+    if os.path.exists(ref):  # the reference's KFP variant, unmodified
+        import importlib.util
+        import json
+        with ktw.install_shims():
+            spec = importlib.util.spec_from_file_location("kfp_preprocessing", ref)
+            mod = importlib.util.module_from_spec(spec)
+            spec.loader.exec_module(mod)
+        with open(os.path.join(os.path.dirname(ref), "schema.json")) as f:
+            cols = {c["name"]: ("float32" if c["type"] == "NUMBER" else "bytes") for c in json.load(f)}
+        plan4 = ktw.trace(mod.preprocess, cols, dense_keys=set(cols))
+        kinds = [type(s).__name__ for s in plan4.specs]
+        assert kinds == ["ZScoreSpec"] * 3 + ["VocabSpec"] * 6 + ["BucketSpec"] * 4 + ["CastSpec"] * 3 + ["RatioLabelSpec"]
+        assert plan4.specs[3].vocab_filename == "vocab_pickup_census_tract" and not plan4.specs[3].as_string
+        cols["pickup_community_area"] = "int64"
+        plan5 = ktw.trace(mod.preprocess, cols, dense_keys=set(cols))
+        assert [s.in_key for s in plan5.specs if getattr(s, "as_string", False)] == ["pickup_community_area"]
