@@ -238,6 +238,53 @@ TXF_API int txf_transform(const txf_op* ops, int nops, int64_t n, txf_stream_t s
 TXF_API int txf_transform_launch_info(int* grid, int* block, int* smem_bytes);
 
 /* ------------------------------------------------------------------------------------------
+ * CSV ingest on the GPU (north_star subsystem 1).  Replaces, for this path, TFX
+ * CsvExampleGen (airflow-dags/taxi_pipeline.py:70-73) and the typed CSV -> Example loop of
+ * notebooks/04_TensorFlow_Model_Analysis.ipynb:222-240: the text of the file, copied to the device
+ * once, becomes int64 / float32 / string columns with validity bitmaps.  Records are lines; fields
+ * may be quoted ("" = escaped quote); an empty unquoted field is a missing value.
+ *   text_dev: 16-byte aligned, with at least 16 readable bytes past nbytes; nbytes < 2^31.
+ *   1. txf_csv_count_lines -> block_lines_dev[ceil(nbytes / txf_csv_block_bytes())] ('\n' per block)
+ *   2. caller: exclusive prefix sum -> block_base_dev (int64); nlines = sum (+1 if the text does
+ *      not end with '\n')
+ *   3. txf_csv_line_starts -> line_start_dev[0 .. sum]; the caller sets line_start[nlines] = nbytes
+ *   4. txf_csv_classify (optional, type inference): ORs TXF_CSV_SEEN_* into col_flags_dev[ncols]
+ *   5. txf_csv_parse: rows [first_line, first_line + nrows) into the columns below
+ *   6. per string column: caller prefix-sums lens into int32 offsets, then txf_csv_copy_strings
+ * status_dev[0] = OR of TXF_CSV_ERR_* over all rows, status_dev[1] = smallest offending line
+ * (the caller initialises them to 0 and UINT64_MAX).  Decimal text becomes the float32 nearest to
+ * the double Python's float() gives, exactly, for up to 19 significant digits and a decimal
+ * exponent within +-22 after folding; longer literals raise TXF_CSV_ERR_PRECISION.
+ * ------------------------------------------------------------------------------------------ */
+#define TXF_CSV_MAX_COLS 64
+enum { TXF_CSV_SKIP = 0, TXF_CSV_I64 = 1, TXF_CSV_F32 = 2, TXF_CSV_BYTES = 3 };
+enum { TXF_CSV_SEEN_VALUE = 1, TXF_CSV_SEEN_INT = 2, TXF_CSV_SEEN_DECIMAL = 4, TXF_CSV_SEEN_TEXT = 8 };
+enum {
+  TXF_CSV_ERR_FIELD_COUNT = 1,   /* a line has more or fewer fields than ncols */
+  TXF_CSV_ERR_QUOTE = 2,         /* unterminated quote, or text after a closing quote */
+  TXF_CSV_ERR_NOT_A_NUMBER = 4,  /* a field of a numeric column is not a number */
+  TXF_CSV_ERR_RANGE = 8,         /* integer outside int64 */
+  TXF_CSV_ERR_PRECISION = 16     /* decimal literal beyond the exactly convertible range */
+};
+typedef struct txf_csv_column {
+  int32_t kind;     /* TXF_CSV_* */
+  int32_t reserved;
+  void* values;     /* int64[nrows] | float[nrows] | uint32 field position[nrows] (strings) */
+  int32_t* lens;    /* strings: field length after un-escaping; else NULL */
+  void* valid;      /* bitmap, ceil(nrows / 32) * 4 bytes, 4-byte aligned; nrows' first row % 256 == 0 */
+} txf_csv_column;
+TXF_API int64_t txf_csv_block_bytes(void);
+TXF_API int txf_csv_count_lines(const uint8_t* text_dev, int64_t nbytes, uint32_t* block_lines_dev, txf_stream_t stream);
+TXF_API int txf_csv_line_starts(const uint8_t* text_dev, int64_t nbytes, const int64_t* block_base_dev,
+                                int64_t* line_start_dev, txf_stream_t stream);
+TXF_API int txf_csv_classify(const uint8_t* text_dev, const int64_t* line_start_dev, int64_t first_line, int64_t nrows,
+                             int ncols, uint32_t* col_flags_dev, uint64_t* status_dev, txf_stream_t stream);
+TXF_API int txf_csv_parse(const uint8_t* text_dev, const int64_t* line_start_dev, int64_t first_line, int64_t nrows,
+                          int ncols, const txf_csv_column* columns, uint64_t* status_dev, txf_stream_t stream);
+TXF_API int txf_csv_copy_strings(const uint8_t* text_dev, const uint32_t* pos_dev, const int32_t* offsets_dev,
+                                 int64_t nrows, uint8_t* pool_dev, txf_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
  * Sibling analyzers / mappers of the workshop notebooks.
  *   min/max analyzer + tft.scale_to_0_1 / scale_by_min_max:
  *     notebooks/03_TensorFlow_Transform.ipynb:148, 03a_TensorFlow_Transform_Advanced.ipynb:323,333

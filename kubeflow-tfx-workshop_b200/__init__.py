@@ -4,6 +4,7 @@
 Public surface:
 
 * ``Table`` / ``NumericColumn`` / ``StringColumn`` -- columnar ingest (host or GPU buffers);
+  ``read_csv`` parses CSV text on the GPU into such a table;
 * ``tf``, ``tft``, ``tft_beam``, ``tf_metadata`` -- stand-ins for the symbols the reference's
   ``preprocessing_fn`` and notebooks touch; ``install_shims()`` binds them into ``sys.modules`` so
   that file runs unmodified;
@@ -26,6 +27,7 @@ from . import tf_metadata, tf_shim, tft_shim
 from .columns import NumericColumn, StringColumn, Table
 from .dist import Comm, shard_range
 from .engine import Engine, TransformState
+from .ingest import read_csv
 from .plan import Plan, trace
 from .state import TFTransformOutput, load_state, save_state
 
@@ -33,7 +35,7 @@ tf = tf_shim
 tft = tft_shim
 
 __all__ = ["Table", "NumericColumn", "StringColumn", "Engine", "TransformState", "Plan", "trace", "Comm", "shard_range",
-           "tf", "tft", "tft_beam", "tf_metadata", "save_state", "load_state", "TFTransformOutput", "install_shims"]
+           "tf", "tft", "tft_beam", "tf_metadata", "save_state", "load_state", "TFTransformOutput", "read_csv", "install_shims"]
 
 _SHIM_MODULES = {
     "tensorflow": tf_shim,

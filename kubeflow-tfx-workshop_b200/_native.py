@@ -42,7 +42,19 @@ class TxfOperand(Structure):
     _fields_ = [("col", c_void_p), ("valid", c_void_p), ("scalar", c_void_p), ("dtype", c_int32), ("reserved", c_int32)]
 
 
+class TxfCsvColumn(Structure):
+    """struct txf_csv_column (include/taxi_xf.h)."""
+
+    _fields_ = [("kind", c_int32), ("reserved", c_int32), ("values", c_void_p), ("lens", c_void_p), ("valid", c_void_p)]
+
+
 ARITH_ADD, ARITH_SUB, ARITH_MUL, ARITH_DIV = range(4)
+CSV_SKIP, CSV_I64, CSV_F32, CSV_BYTES = range(4)
+CSV_SEEN_VALUE, CSV_SEEN_INT, CSV_SEEN_DECIMAL, CSV_SEEN_TEXT = 1, 2, 4, 8
+CSV_ERRORS = {1: "a line has more or fewer fields than the header", 2: "unterminated quote or text after a closing quote",
+              4: "a field of a numeric column is not a number", 8: "integer outside int64",
+              16: "decimal literal too long to convert exactly (more than 19 significant digits or exponent beyond +-22)"}
+TXF_CSV_MAX_COLS = 64
 
 if not os.path.exists(LIB_PATH):
     raise ImportError(
@@ -98,6 +110,12 @@ _SIGNATURES = {
     "txf_i64_format_lengths": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
     "txf_i64_format_write": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p]),
     "txf_map_scale_minmax": (c_int, [POINTER(TxfOperand), c_void_p, c_float, c_float, c_void_p, c_int64, c_void_p]),
+    "txf_csv_block_bytes": (c_int64, []),
+    "txf_csv_count_lines": (c_int, [c_void_p, c_int64, c_void_p, c_void_p]),
+    "txf_csv_line_starts": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p]),
+    "txf_csv_classify": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int, c_void_p, c_void_p, c_void_p]),
+    "txf_csv_parse": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int, POINTER(TxfCsvColumn), c_void_p, c_void_p]),
+    "txf_csv_copy_strings": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
     "txf_fingerprint64_batch": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
 }
 

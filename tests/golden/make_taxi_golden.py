@@ -93,3 +93,8 @@ def main():
 
 if __name__ == "__main__":
     main()
+
+
+# tests/golden/taxi_head200.csv: header + first 200 data lines of the same file, byte for byte
+# (`head -201 data.csv`), for the GPU CSV-ingest test: parsing it must reproduce rows [0, 200) of
+# the columns stored in taxi_15000.npz.

@@ -355,3 +355,44 @@ def test_trace_notebook03_and_kfp_variants(ktw):
         cols["pickup_community_area"] = "int64"
         plan5 = ktw.trace(mod.preprocess, cols, dense_keys=set(cols))
         assert [s.in_key for s in plan5.specs if getattr(s, "as_string", False)] == ["pickup_community_area"]
+
+
+def test_exact_decimal_to_double_compiled_for_host(tmp_path):
+    """csrc/decimal.cuh is __host__ __device__: the big-integer conversion the CSV ingest uses for
+    long literals must give Python's float() bit for bit (it is correctly rounded)."""
+    src = tmp_path / "dec.cu"
+    src.write_text(r'''
+#include <cstdio>
+#include <cstring>
+#include "decimal.cuh"
+int main() {
+  unsigned long long m; int e;
+  while (scanf("%llu %d", &m, &e) == 2) {
+    double d = txf::decimal_to_double_exact(m, e);
+    unsigned long long u; memcpy(&u, &d, 8);
+    printf("%016llx\n", u);
+  }
+}
+''')
+    exe = tmp_path / "dec"
+    subprocess.run(["nvcc", "-O1", "-std=c++17", "-I", os.path.join(ROOT, "kubeflow-tfx-workshop_b200", "csrc"), str(src), "-o", str(exe)],
+                   check=True, capture_output=True)
+    rng = np.random.default_rng(11)
+    cases = [(1, 0), (1, -77), (1, 77), (2 ** 64 - 1, -77), (2 ** 64 - 1, 0), (9007199254740993, 0), (9007199254740993, 5),
+             (5, -1), (4503599627370497, -1), (17976931348623157, 60)]
+    for _ in range(60_000):
+        digits = int(rng.integers(1, 20))
+        m = int(rng.integers(1, 10)) * 10 ** (digits - 1) + (int(rng.integers(0, 10 ** (digits - 1))) if digits > 1 else 0)
+        cases.append((min(m, 2 ** 64 - 1), int(rng.integers(-77, 78))))
+    import struct
+    for _ in range(20_000):  # 17-digit reprs of random doubles: must round-trip
+        x = float(np.ldexp(float(rng.integers(1, 2 ** 53)), int(rng.integers(-200, 150))))
+        mant, exp = ("%.16e" % x).split("e")
+        m, e = int(mant.replace(".", "")), int(exp) - 16
+        if -77 <= e <= 77:
+            cases.append((m, e))
+    out = subprocess.run([str(exe)], input="".join(f"{m} {e}\n" for m, e in cases), text=True, capture_output=True, check=True).stdout.split()
+    assert len(out) == len(cases)
+    for (m, e), got in zip(cases, out):
+        want = struct.pack(">d", float(f"{m}e{e}")).hex()
+        assert got == want, (m, e, got, want)
