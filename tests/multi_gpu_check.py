@@ -77,6 +77,33 @@ def main():
         if rank == 0:
             print(f"multi-gpu parity ok: world={world} rows={n} fixed_exchange={fixed} tiny={tiny} "
                   f"quantile path={eng.last_quantile_path}", flush=True)
+    # sibling analyzers across ranks: min/max merge, mean scalar, as_string vocabulary
+    tf, tft = ktw.tf, ktw.tft
+
+    def sib(inputs):
+        fare = inputs["fare"]
+        return {"unit": tft.scale_to_0_1(fare), "centered": fare - tft.mean(fare),
+                "area": tft.compute_and_apply_vocabulary(tf.as_string(inputs["pickup_community_area"]), top_k=20, num_oov_buckets=3)}
+
+    schema = {"fare": "float32", "pickup_community_area": "int64"}
+    eng = ktw.Engine(ktw.trace(sib, schema, dense_keys=set(schema)), device=f"cuda:{local}", comm=comm)
+    shard = shard_host.select(list(schema)).to(f"cuda:{local}")
+    out, state = eng.analyze_and_transform(shard)
+    torch.cuda.synchronize()
+    cols = helpers.oracle_from_table(synth.taxi_table(n, backend="numpy").select(list(schema)))
+    fare = O.fill_in_missing(cols["fare"])
+    mn, mx = O.min_max(fare)
+    assert np.array_equal(np.array(state.min_max_of("fare"), np.float32).view(np.uint32), np.array([mn, mx], np.float32).view(np.uint32))
+    got = out["unit"].values.cpu().numpy()
+    assert np.array_equal(got.view(np.uint32), O.scale_by_min_max(fare, mn, mx)[lo:hi].view(np.uint32))
+    mean = np.float32(state.mean_var_of("fare")[0])
+    assert abs(float(mean) - float(O.mean_f32(fare))) <= 1e-6 * abs(float(mean))
+    assert np.array_equal(out["centered"].values.cpu().numpy().view(np.uint32), O.arith_f32("sub", fare, mean)[lo:hi].view(np.uint32))
+    strings = [str(int(v)).encode() for v in O.fill_in_missing(cols["pickup_community_area"]).tolist()]
+    vocab = O.finalize_vocabulary(O.vocab_counts(strings), top_k=20)
+    assert np.array_equal(out["area"].values.cpu().numpy(), O.apply_vocabulary(strings, vocab, num_oov_buckets=3)[lo:hi])
+    if rank == 0:
+        print(f"multi-gpu sibling parity ok: world={world} rows={n}", flush=True)
     dist.barrier()
     dist.destroy_process_group()
 

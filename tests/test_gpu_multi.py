@@ -18,3 +18,4 @@ def test_two_rank_nccl_parity():
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
     assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
     assert out.stdout.count("multi-gpu parity ok") == 4
+    assert out.stdout.count("multi-gpu sibling parity ok") == 1
