@@ -285,6 +285,34 @@ TXF_API int txf_csv_copy_strings(const uint8_t* text_dev, const uint32_t* pos_de
                                  int64_t nrows, uint8_t* pool_dev, txf_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------
+ * tf.Example / TFRecord encode on the GPU (egress).  Replaces, for this path,
+ * ExampleProtoCoder.encode + WriteToTFRecord (notebooks/03a_TensorFlow_Transform_Advanced.ipynb:445-455;
+ * the files are read back at airflow-dags/taxi_utils.py:79-83,260-281).  Row i of the given columns
+ * becomes one framed record: u64 length, u32 masked CRC-32C of the length, the serialized Example
+ * (map entries in the order of `feats`, which the caller sorts by name -- protobuf's deterministic
+ * order), u32 masked CRC-32C of the data.  A missing cell is an empty value list.
+ *   1. txf_example_sizes -> sizes_dev[n] (bytes of each framed record)
+ *   2. caller: exclusive prefix sum -> offsets_dev[n + 1]
+ *   3. txf_example_encode -> out_dev[offsets[n]]
+ * names_dev holds the UTF-8 feature names back to back; name_off/name_len index it.
+ * ------------------------------------------------------------------------------------------ */
+#define TXF_EX_MAX_FEATURES 64
+#define TXF_EX_BYTES 2 /* kind of a string feature (numbers use TXF_F32 / TXF_I64) */
+typedef struct txf_example_feature {
+  int32_t kind;       /* TXF_F32 | TXF_I64 | TXF_EX_BYTES */
+  int32_t name_off;
+  int32_t name_len;
+  int32_t reserved;
+  const void* values; /* float[n] | int64[n] | int32 offsets[n + 1] */
+  const void* pool;   /* strings: byte pool */
+  const void* valid;  /* validity bitmap or NULL */
+} txf_example_feature;
+TXF_API int txf_example_sizes(const txf_example_feature* feats, int nfeat, int64_t n, int64_t* sizes_dev,
+                              txf_stream_t stream);
+TXF_API int txf_example_encode(const txf_example_feature* feats, int nfeat, const uint8_t* names_dev, int64_t n,
+                               const int64_t* offsets_dev, uint8_t* out_dev, txf_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
  * Sibling analyzers / mappers of the workshop notebooks.
  *   min/max analyzer + tft.scale_to_0_1 / scale_by_min_max:
  *     notebooks/03_TensorFlow_Transform.ipynb:148, 03a_TensorFlow_Transform_Advanced.ipynb:323,333

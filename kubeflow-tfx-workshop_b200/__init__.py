@@ -27,6 +27,7 @@ from . import tf_metadata, tf_shim, tft_shim
 from .columns import NumericColumn, StringColumn, Table
 from .dist import Comm, shard_range
 from .engine import Engine, TransformState
+from .egress import encode_tfrecord, write_tfrecord
 from .ingest import read_csv
 from .plan import Plan, trace
 from .state import TFTransformOutput, load_state, save_state
@@ -35,7 +36,7 @@ tf = tf_shim
 tft = tft_shim
 
 __all__ = ["Table", "NumericColumn", "StringColumn", "Engine", "TransformState", "Plan", "trace", "Comm", "shard_range",
-           "tf", "tft", "tft_beam", "tf_metadata", "save_state", "load_state", "TFTransformOutput", "read_csv", "install_shims"]
+           "tf", "tft", "tft_beam", "tf_metadata", "save_state", "load_state", "TFTransformOutput", "read_csv", "encode_tfrecord", "write_tfrecord", "install_shims"]
 
 _SHIM_MODULES = {
     "tensorflow": tf_shim,

@@ -48,6 +48,15 @@ class TxfCsvColumn(Structure):
     _fields_ = [("kind", c_int32), ("reserved", c_int32), ("values", c_void_p), ("lens", c_void_p), ("valid", c_void_p)]
 
 
+class TxfExampleFeature(Structure):
+    """struct txf_example_feature (include/taxi_xf.h)."""
+
+    _fields_ = [("kind", c_int32), ("name_off", c_int32), ("name_len", c_int32), ("reserved", c_int32),
+                ("values", c_void_p), ("pool", c_void_p), ("valid", c_void_p)]
+
+
+TXF_EX_BYTES = 2
+TXF_EX_MAX_FEATURES = 64
 ARITH_ADD, ARITH_SUB, ARITH_MUL, ARITH_DIV = range(4)
 CSV_SKIP, CSV_I64, CSV_F32, CSV_BYTES = range(4)
 CSV_SEEN_VALUE, CSV_SEEN_INT, CSV_SEEN_DECIMAL, CSV_SEEN_TEXT = 1, 2, 4, 8
@@ -116,6 +125,8 @@ _SIGNATURES = {
     "txf_csv_classify": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int, c_void_p, c_void_p, c_void_p]),
     "txf_csv_parse": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int, POINTER(TxfCsvColumn), c_void_p, c_void_p]),
     "txf_csv_copy_strings": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
+    "txf_example_sizes": (c_int, [POINTER(TxfExampleFeature), c_int, c_int64, c_void_p, c_void_p]),
+    "txf_example_encode": (c_int, [POINTER(TxfExampleFeature), c_int, c_void_p, c_int64, c_void_p, c_void_p, c_void_p]),
     "txf_fingerprint64_batch": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
 }
 

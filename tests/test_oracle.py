@@ -151,3 +151,17 @@ def test_sharded_analyze_merges_to_whole():
     for k in O.DENSE_FLOAT_KEYS:
         assert merged["zscore"][k][0] == pytest.approx(whole["zscore"][k][0], rel=1e-6)
         assert merged["zscore"][k][1] == pytest.approx(whole["zscore"][k][1], rel=1e-6)
+
+
+def test_example_oracle_layout_and_crc():
+    """oracle/example_oracle.py: CRC-32C check value and the wire layout the GPU encoder restates."""
+    import sys
+    sys.path.insert(0, helpers.ROOT)
+    from oracle import example_oracle as E
+    assert E.crc32c(b"123456789") == 0xE3069283  # published check value (Castagnoli polynomial)
+    ex = E.make_example({"b": ("float32", 1.5), "a": ("int64", -3), "s": ("bytes", b"hi"), "m": ("float32", None)})
+    data = ex.SerializeToString(deterministic=True)
+    assert data.hex() == ("0a3a" "0a13" "0a0161" "120e" "1a0c0a0a" "fdffffffffffffffff01" "0a0d" "0a0162" "1208" "12060a04" "0000c03f"
+                          "0a07" "0a016d" "1202" "1200" "0a0b" "0a0173" "1206" "0a040a02" "6869")
+    rec = E.frame(data)
+    assert len(rec) == len(data) + 16 and E.decode_tfrecord(rec + rec)[1].features.feature["a"].int64_list.value[0] == -3

@@ -1,4 +1,4 @@
-"""Throughput of the GPU CSV ingest next to the host readers, on taxi-shaped text.
+"""Throughput of the GPU CSV ingest and tf.Example/TFRecord encode next to the host readers, on taxi-shaped text.
 
     python tools/bench_ingest.py [--mb 512] [--reps 5]
 
@@ -59,6 +59,10 @@ def main():
     ms_e2e = timed(lambda: ktw.read_csv(host, schema=schema))
     out_bytes = table.nbytes()
 
+    sub = ktw.Table({k: c.slice(0, 1 << 20) if c.kind == "numeric" else c for k, c in table.items() if c.kind == "numeric"})
+    ms_enc = timed(lambda: ktw.encode_tfrecord(sub))
+    enc_bytes = int(ktw.encode_tfrecord(sub)[1][-1].item())
+
     import pyarrow.csv as pacsv
     t0 = time.perf_counter()
     pacsv.read_csv(io.BytesIO(text))
@@ -78,6 +82,8 @@ def main():
         "gpu_parse_inferred": {"ms": ms_infer, "GBps_text": nbytes / ms_infer / 1e6, "rows_per_s": nrows / ms_infer * 1e3},
         "gpu_parse_typed": {"ms": ms_typed, "GBps_text": nbytes / ms_typed / 1e6, "rows_per_s": nrows / ms_typed * 1e3},
         "gpu_e2e_from_pinned_host": {"ms": ms_e2e, "GBps_text": nbytes / ms_e2e / 1e6, "rows_per_s": nrows / ms_e2e * 1e3},
+        "gpu_tfrecord_encode": {"rows": len(sub), "features": len(list(sub.keys())), "ms": ms_enc, "out_mb": enc_bytes / 1e6,
+                                "rows_per_s": len(sub) / ms_enc * 1e3, "GBps_out": enc_bytes / ms_enc / 1e6},
         "pyarrow_host": {"s": t_arrow, "GBps_text": nbytes / t_arrow / 1e9, "rows_per_s": nrows / t_arrow, "threads": os.cpu_count()},
         "python_row_loop": {"rows": sample_rows, "s": t_py, "rows_per_s": sample_rows / t_py, "threads": 1},
     }))
