@@ -155,8 +155,6 @@ class Engine:
                 self.minmax_keys.append(k)
         self.vocab_specs: Dict[Tuple, VocabSpec] = {}
         for s in plan.of(VocabSpec) + plan.of(VocabOnlySpec):
-            if s.frequency_threshold is not None:
-                raise NotImplementedError("frequency_threshold is not supported yet")
             self.vocab_specs.setdefault(_vocab_key(s), s)
         self._static_vocabs: Dict[str, VocabResult] = {}   # StaticVocabSpec.out_key -> lookup built from its terms
         self._formatted: Dict[Tuple, Tuple[Table, StringColumn]] = {}  # (id(table), feature) -> tf.as_string column
@@ -714,8 +712,16 @@ class Engine:
             kept = int(ctrl_host[3])
         tag, table, arena, ctrl, ent, counts = (pend[k] for k in ("tag", "table", "arena", "ctrl", "ent", "counts"))
         k = kept if spec.top_k is None else min(spec.top_k, kept)
-        sel, m = ent, kept
-        if kept > k:
+        if spec.frequency_threshold and kept:
+            # terms seen fewer than frequency_threshold times never enter the vocabulary; the list is
+            # ordered by descending count, so they can only shorten it
+            fthr = torch.tensor([min(int(spec.frequency_threshold), 0x7FFFFFFF)], dtype=torch.int32, device=self.device)
+            scratch_sel = self._buf(f"{tag}_fsel", pend["cap"], torch.int32)
+            nat.call("txf_vocab_filter_ge", ent.data_ptr(), counts.data_ptr(), kept, fthr.data_ptr(), scratch_sel.data_ptr(),
+                     ctrl.data_ptr(), s)
+            k = min(k, int(ctrl[5].item()))
+        sel, m = ent, (kept if k else 0)
+        if kept > k and k > 0:
             # count cut-off: the k-th largest count (exact), then only entries >= it need ordering
             rank = torch.tensor([[kept - k + 1]], dtype=torch.int64, device=self.device)
             cptr = nat.ptr_array([counts.data_ptr()])

@@ -308,6 +308,33 @@ def test_vocabulary_stress(ktw, n_distinct, top_k, oov):
     assert np.array_equal(out["s_id"].values.cpu().numpy(), want_ids)
 
 
+@pytest.mark.parametrize("top_k,thr", [(None, 3), (1000, 5), (10, 2), (None, 10 ** 9), (50, 1)])
+def test_vocabulary_frequency_threshold(ktw, top_k, thr):
+    """frequency_threshold keeps terms seen at least that many times (tft 0.13 keyword), before top_k."""
+    tf, tft = ktw.tf, ktw.tft
+    rng = np.random.default_rng(thr)
+    terms = _stress_terms(4000, rng)
+    counts = np.maximum(1, 2000 // (np.arange(4000) + 1)).astype(np.int64)
+    rows = np.repeat(np.arange(4000), counts)
+    rng.shuffle(rows)
+    col = O.StrCol.from_list([terms[i] for i in rows])
+    host = helpers.table_from_oracle({"s": col}, ktw)
+
+    def fn(inputs):
+        x = inputs["s"]
+        d = tf.squeeze(tf.sparse.to_dense(tf.SparseTensor(x.indices, x.values, [x.dense_shape[0], 1]), ""), axis=1)
+        return {"s_id": tft.compute_and_apply_vocabulary(d, top_k=top_k, frequency_threshold=thr, num_oov_buckets=4)}
+
+    eng = ktw.Engine(ktw.trace(fn, host.schema()))
+    out, state = eng.analyze_and_transform(host.to("cuda"))
+    filled = O.fill_in_missing(col)
+    want_vocab = O.finalize_vocabulary(O.vocab_counts(filled), top_k=top_k, frequency_threshold=thr)
+    assert state.vocabs[("s", top_k, thr)].terms() == want_vocab
+    want_ids = O.apply_vocabulary(filled, want_vocab, 4) if want_vocab != [O.EMPTY_VOCAB_SENTINEL] else None
+    if want_ids is not None:
+        assert np.array_equal(out["s_id"].values.cpu().numpy(), want_ids)
+
+
 def test_vocabulary_empty_and_all_missing(ktw):
     col = O.StrCol.from_list([None, b"", None, b"\n", None])
     host = helpers.table_from_oracle({"s": col}, ktw)
