@@ -118,3 +118,91 @@ def test_config5_eight_float_columns(ktw, nb):
         ids = torch.bucketize(data[k], got, right=True)
         assert torch.equal(out[k + "_b"].values, ids), (k, nb)
         del srt, ids
+
+
+def test_config2_hundred_million_rows(ktw):
+    """BASELINE configs[1] at full size: 100 M synthetic taxi rows on one GPU.  Every analyzer result
+    and every output cell is checked on the device against an independent torch computation (sort,
+    bincount, bucketize, fp32 arithmetic); the vocabulary order comes from the oracle's rule applied
+    to the exact counts."""
+    from kubeflow_tfx_workshop_b200 import synth
+    dev = "cuda"
+    n = 100_000_000
+    fn = helpers.load_example_preprocessing_fn(ktw).preprocessing_fn
+    table = synth.taxi_table(n)
+    eng = ktw.Engine(ktw.trace(fn, synth.TAXI_SCHEMA))
+    out, state = eng.analyze_and_transform(table)
+    torch.cuda.synchronize()
+
+    def filled(key):
+        c = table[key]
+        if c.valid is None:
+            return c.values
+        bits = c.valid[: (n + 7) // 8]
+        present = ((bits.unsqueeze(1) >> torch.arange(8, device=dev, dtype=torch.uint8)) & 1).reshape(-1)[:n].bool()
+        return torch.where(present, c.values, torch.zeros_like(c.values))
+
+    # ---- z-score: moments against fp64 torch reductions, outputs against fp32 torch arithmetic ----
+    for key in ("trip_miles", "fare", "trip_seconds"):
+        x = filled(key)
+        xd = x.double()
+        mean, var = float(xd.mean()), float(xd.var(unbiased=False))
+        m, v = state.mean_var_of(key)
+        assert abs(m - mean) <= 1e-6 * abs(mean) and abs(v - var) <= 1e-6 * var, (key, m, mean, v, var)
+        mt = torch.tensor(m, dtype=torch.float32, device=dev)
+        want = (x.float() - mt) / torch.sqrt(torch.tensor(v, dtype=torch.float32, device=dev))
+        got = out[key + "_xf"].values
+        atol = 4 * float(np.spacing(np.float32(abs(m)) + np.float32(1))) / float(np.sqrt(np.float32(v)))
+        assert torch.allclose(got, want, rtol=1e-6, atol=atol), key
+        assert abs(float(got.double().mean())) < 1e-3 and abs(float(got.double().var(unbiased=False)) - 1.0) < 1e-3, key
+        del x, xd, want
+    # ---- bucketize: exact order statistics and upper_bound ids --------------------------------------
+    ranks = torch.tensor([-(-i * n // 10) for i in range(1, 10)], dtype=torch.int64, device=dev)
+    res = state.buckets[10]
+    for key in ("pickup_latitude", "pickup_longitude", "dropoff_latitude", "dropoff_longitude"):
+        x = filled(key)
+        srt = torch.sort(x).values
+        want_b = torch.unique_consecutive(srt[ranks - 1])
+        got_b = torch.from_numpy(res.boundaries_of(key)).to(dev)
+        assert got_b.numel() == want_b.numel() and torch.equal(got_b.view(torch.int32), want_b.view(torch.int32)), key
+        assert torch.equal(out[key + "_xf"].values, torch.bucketize(x, got_b, right=True)), key
+        del x, srt
+    # ---- vocabularies: regenerate the term index of every row, count exactly, order by the oracle's rule
+    xp = synth._Th(dev)
+    pidx = torch.empty(n, dtype=torch.int64, device=dev)
+    cidx = torch.empty(n, dtype=torch.int64, device=dev)
+    cmiss = torch.empty(n, dtype=torch.bool, device=dev)
+    for lo in range(0, n, 1 << 23):
+        hi = min(lo + (1 << 23), n)
+        rows = xp.rows(lo, hi)
+        r = synth._draw(xp, rows, synth.SEED, "payment_type") % 10000
+        p = (r >= synth._PAYMENT_THRESHOLDS[0]) * 1
+        for t in synth._PAYMENT_THRESHOLDS[1:]:
+            p = p + (r >= t) * 1
+        pidx[lo:hi] = p
+        cidx[lo:hi] = synth._skewed_index(xp, rows, synth.SEED, "company", 0, synth.N_COMPANIES)
+        cmiss[lo:hi] = synth._draw(xp, rows, synth.SEED, "company", 2) % 100 < 34
+    empty_id = lambda size: size + O.fingerprint64_c(b"") % 10  # a missing cell is '' -> out of vocabulary
+    for key, idx, miss, names in (("payment_type", pidx, None, synth.PAYMENT_TYPES), ("company", cidx, cmiss, synth.company_names())):
+        live = idx if miss is None else idx[~miss]
+        counts = torch.bincount(live, minlength=len(names)).cpu().tolist()
+        want_vocab = O.finalize_vocabulary({t: c for t, c in zip(names, counts) if c}, top_k=1000)
+        got_vocab = state.vocabs[(key, 1000, None)].terms()
+        assert got_vocab == want_vocab, key
+        rank = {t: i for i, t in enumerate(want_vocab)}
+        lut = torch.tensor([rank.get(t, -7) for t in names], dtype=torch.int64, device=dev)  # names that never occur are never looked up
+        want_ids = lut[idx]
+        if miss is not None:
+            want_ids = torch.where(miss, torch.full_like(want_ids, empty_id(len(want_vocab))), want_ids)
+        assert torch.equal(out[key + "_xf"].values, want_ids), key
+        del want_ids
+    # ---- pass-through categoricals, the all-missing string feature, and the label ------------------
+    for key in ("trip_start_hour", "trip_start_day", "trip_start_month", "pickup_community_area", "dropoff_community_area",
+                "dropoff_census_tract"):
+        assert torch.equal(out[key + "_xf"].values, filled(key)), key
+    pct = out["pickup_census_tract_xf"]
+    assert int(pct.offsets.abs().max()) == 0 and pct.offsets.numel() == n + 1
+    fare, tips = filled("fare"), filled("tips")
+    want = (tips > fare * torch.tensor(0.2, dtype=torch.float32, device=dev)).to(torch.int64)
+    assert torch.equal(out["tips_xf"].values, want)
+    assert 0.05 < float(want.float().mean()) < 0.5
