@@ -12,7 +12,8 @@
 //
 // which is byte for byte what protobuf's deterministic serialisation of the same Example gives
 // (tests/test_gpu_egress.py checks that against the protobuf runtime).  Two kernels, one thread per
-// row: sizes (the caller prefix-sums them), then the bytes.
+// row: sizes (the caller prefix-sums them), then the bytes -- written into shared memory, 128 records
+// per CTA, and copied out with coalesced 16-byte stores.
 #include "common.cuh"
 
 namespace txf {
@@ -33,11 +34,6 @@ __device__ __forceinline__ uint32_t varint_len(unsigned long long v) {
   uint32_t n = 1;
   while (v >= 0x80ULL) { v >>= 7; ++n; }
   return n;
-}
-__device__ __forceinline__ uint8_t* put_varint(uint8_t* p, unsigned long long v) {
-  while (v >= 0x80ULL) { *p++ = static_cast<uint8_t>(v) | 0x80u; v >>= 7; }
-  *p++ = static_cast<uint8_t>(v);
-  return p;
 }
 
 // length of the Feature message of one cell
@@ -74,82 +70,113 @@ __global__ void example_sizes_kernel(ExFeats fs, int64_t n, int64_t* __restrict_
   sizes[row] = 16 + static_cast<int64_t>(example_len(fs, row, fl));
 }
 
-// CRC-32C (Castagnoli), reflected, one byte per step from a table in shared memory
-__device__ __forceinline__ uint32_t crc32c_bytes(const uint32_t* tab, const uint8_t* p, uint32_t n) {
-  uint32_t c = 0xFFFFFFFFu;
-  for (uint32_t i = 0; i < n; ++i) c = tab[(c ^ p[i]) & 0xFFu] ^ (c >> 8);
-  return ~c;
-}
+// CRC-32C (Castagnoli), reflected, one byte per step from a table in shared memory; the running
+// value is updated as each byte is written, so nothing is read back.
+struct Emitter {
+  uint8_t* p;
+  uint32_t crc;
+  const uint32_t* tab;
+  __device__ __forceinline__ void put(uint32_t b) {
+    *p++ = static_cast<uint8_t>(b);
+    crc = tab[(crc ^ b) & 0xFFu] ^ (crc >> 8);
+  }
+  __device__ __forceinline__ void varint(unsigned long long v) {
+    while (v >= 0x80ULL) { put((static_cast<uint32_t>(v) & 0x7Fu) | 0x80u); v >>= 7; }
+    put(static_cast<uint32_t>(v));
+  }
+};
 __device__ __forceinline__ uint32_t mask_crc(uint32_t crc) { return ((crc >> 15) | (crc << 17)) + 0xa282ead8u; }
 
-__global__ void __launch_bounds__(256) example_encode_kernel(ExFeats fs, const uint8_t* __restrict__ names, int64_t n,
-                                                             const int64_t* __restrict__ offsets, uint8_t* __restrict__ out) {
+constexpr int kExRows = 128;               // rows (= threads) per CTA
+constexpr int kExStageBytes = 56 * 1024;   // records of one CTA staged in shared memory, then copied out coalesced
+
+__global__ void __launch_bounds__(kExRows) example_encode_kernel(ExFeats fs, const uint8_t* __restrict__ names, int64_t n,
+                                                                 const int64_t* __restrict__ offsets, uint8_t* __restrict__ out) {
+  extern __shared__ __align__(16) uint8_t s_stage[];
   __shared__ uint32_t tab[256];
-  {
-    uint32_t c = threadIdx.x;
+  for (int t = threadIdx.x; t < 256; t += kExRows) {
+    uint32_t c = t;
     for (int k = 0; k < 8; ++k) c = (c & 1u) ? (c >> 1) ^ 0x82F63B78u : (c >> 1);
-    tab[threadIdx.x] = c;
+    tab[t] = c;
   }
+  const int64_t r0 = static_cast<int64_t>(blockIdx.x) * kExRows;
+  const int64_t r1 = r0 + kExRows < n ? r0 + kExRows : n;
+  const int64_t g0 = offsets[r0], g1 = offsets[r1];
+  const uint32_t skew = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(out + g0) & 15u);  // same 16-byte phase in both memories
+  const bool staged = g1 - g0 + skew <= kExStageBytes;
   __syncthreads();
-  const int64_t row = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
-  if (row >= n) return;
-  uint8_t* rec = out + offsets[row];
-  uint32_t features_len;
-  const uint32_t elen = example_len(fs, row, features_len);
-  // frame header
-  const unsigned long long len64 = elen;
-  for (int i = 0; i < 8; ++i) rec[i] = static_cast<uint8_t>(len64 >> (8 * i));
-  const uint32_t hcrc = mask_crc(crc32c_bytes(tab, rec, 8));
-  for (int i = 0; i < 4; ++i) rec[8 + i] = static_cast<uint8_t>(hcrc >> (8 * i));
-  uint8_t* data = rec + 12;
-  uint8_t* p = data;
-  *p++ = 0x0A;
-  p = put_varint(p, features_len);
-  for (int i = 0; i < fs.n; ++i) {
-    const ExFeat& f = fs.f[i];
-    uint32_t inner;
-    const uint32_t fl = feature_len(f, row, inner);
-    const uint32_t entry = 1u + varint_len(f.name_len) + f.name_len + 1u + varint_len(fl) + fl;
-    *p++ = 0x0A;
-    p = put_varint(p, entry);
-    *p++ = 0x0A;
-    p = put_varint(p, f.name_len);
-    for (int k = 0; k < f.name_len; ++k) *p++ = names[f.name_off + k];
-    *p++ = 0x12;
-    p = put_varint(p, fl);
-    const bool has = row_valid(f.valid, row);
-    if (f.kind == TXF_F32) {
-      *p++ = 0x12;
-      p = put_varint(p, inner);
-      if (has) {
-        const uint32_t u = __float_as_uint(static_cast<const float*>(f.values)[row]);
-        *p++ = 0x0A; *p++ = 4;
-        for (int k = 0; k < 4; ++k) *p++ = static_cast<uint8_t>(u >> (8 * k));
-      }
-    } else if (f.kind == TXF_I64) {
-      *p++ = 0x1A;
-      p = put_varint(p, inner);
-      if (has) {
-        const unsigned long long v = static_cast<unsigned long long>(static_cast<const long long*>(f.values)[row]);
-        *p++ = 0x0A;
-        p = put_varint(p, varint_len(v));
-        p = put_varint(p, v);
-      }
-    } else {
-      *p++ = 0x0A;
-      p = put_varint(p, inner);
-      if (has) {
-        const int32_t* off = static_cast<const int32_t*>(f.values);
-        const uint32_t sl = static_cast<uint32_t>(off[row + 1] - off[row]);
-        *p++ = 0x0A;
-        p = put_varint(p, sl);
-        const uint8_t* src = f.pool + off[row];
-        for (uint32_t k = 0; k < sl; ++k) *p++ = src[k];
+  const int64_t row = r0 + threadIdx.x;
+  if (row < r1) {
+    uint8_t* rec = staged ? s_stage + skew + (offsets[row] - g0) : out + offsets[row];
+    uint32_t features_len;
+    const uint32_t elen = example_len(fs, row, features_len);
+    Emitter e{rec, 0xFFFFFFFFu, tab};
+    for (int i = 0; i < 8; ++i) e.put(i < 4 ? (elen >> (8 * i)) & 0xFFu : 0u);  // u64 length (records are < 4 GiB)
+    const uint32_t hcrc = mask_crc(~e.crc);
+    for (int i = 0; i < 4; ++i) e.put((hcrc >> (8 * i)) & 0xFFu);
+    e.crc = 0xFFFFFFFFu;
+    e.put(0x0A);
+    e.varint(features_len);
+    for (int i = 0; i < fs.n; ++i) {
+      const ExFeat& f = fs.f[i];
+      uint32_t inner;
+      const uint32_t fl = feature_len(f, row, inner);
+      const uint32_t entry = 1u + varint_len(f.name_len) + f.name_len + 1u + varint_len(fl) + fl;
+      e.put(0x0A);
+      e.varint(entry);
+      e.put(0x0A);
+      e.varint(f.name_len);
+      for (int k = 0; k < f.name_len; ++k) e.put(names[f.name_off + k]);
+      e.put(0x12);
+      e.varint(fl);
+      const bool has = row_valid(f.valid, row);
+      if (f.kind == TXF_F32) {
+        e.put(0x12);
+        e.varint(inner);
+        if (has) {
+          const uint32_t u = __float_as_uint(static_cast<const float*>(f.values)[row]);
+          e.put(0x0A); e.put(4);
+          for (int k = 0; k < 4; ++k) e.put((u >> (8 * k)) & 0xFFu);
+        }
+      } else if (f.kind == TXF_I64) {
+        e.put(0x1A);
+        e.varint(inner);
+        if (has) {
+          const unsigned long long v = static_cast<unsigned long long>(static_cast<const long long*>(f.values)[row]);
+          e.put(0x0A);
+          e.varint(varint_len(v));
+          e.varint(v);
+        }
+      } else {
+        e.put(0x0A);
+        e.varint(inner);
+        if (has) {
+          const int32_t* off = static_cast<const int32_t*>(f.values);
+          const uint32_t sl = static_cast<uint32_t>(off[row + 1] - off[row]);
+          e.put(0x0A);
+          e.varint(sl);
+          const uint8_t* src = f.pool + off[row];
+          for (uint32_t k = 0; k < sl; ++k) e.put(src[k]);
+        }
       }
     }
+    const uint32_t dcrc = mask_crc(~e.crc);
+    for (int i = 0; i < 4; ++i) *e.p++ = static_cast<uint8_t>(dcrc >> (8 * i));
   }
-  const uint32_t dcrc = mask_crc(crc32c_bytes(tab, data, elen));
-  for (int i = 0; i < 4; ++i) p[i] = static_cast<uint8_t>(dcrc >> (8 * i));
+  if (!staged) return;
+  __syncthreads();
+  // coalesced copy-out: ragged head up to the first 16-byte boundary, 16-byte body, ragged tail
+  uint8_t* dst = out + g0 - skew;  // 16-byte aligned; byte j of the stage goes to dst[j]
+  const int64_t lo = skew, hi = skew + (g1 - g0);
+  const int64_t body0 = (lo + 15) & ~15LL, body1 = hi & ~15LL;
+  if (body0 >= body1) {
+    for (int64_t j = lo + threadIdx.x; j < hi; j += kExRows) dst[j] = s_stage[j];
+    return;
+  }
+  for (int64_t j = lo + threadIdx.x; j < body0; j += kExRows) dst[j] = s_stage[j];
+  for (int64_t j = body0 + threadIdx.x * 16LL; j < body1; j += kExRows * 16LL)
+    __stcs(reinterpret_cast<uint4*>(dst + j), *reinterpret_cast<const uint4*>(s_stage + j));
+  for (int64_t j = body1 + threadIdx.x; j < hi; j += kExRows) dst[j] = s_stage[j];
 }
 
 static int fill_feats(const txf_example_feature* feats, int nfeat, ExFeats* d) {
@@ -191,8 +218,9 @@ int txf_example_encode(const txf_example_feature* feats, int nfeat, const uint8_
   if (rc) return rc;
   TXF_REQUIRE(names_dev && offsets_dev && out_dev && n >= 0 && n < (1LL << 31), "example_encode: bad arguments");
   if (n == 0) return TXF_OK;
-  example_encode_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(d, names_dev, n, offsets_dev,
-                                                                                                            out_dev);
+  TXF_CUDA(cudaFuncSetAttribute(example_encode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kExStageBytes));
+  example_encode_kernel<<<static_cast<unsigned>((n + kExRows - 1) / kExRows), kExRows, kExStageBytes, static_cast<cudaStream_t>(stream)>>>(
+      d, names_dev, n, offsets_dev, out_dev);
   TXF_LAUNCH_CHECK();
   count_launch(1);
   return TXF_OK;
