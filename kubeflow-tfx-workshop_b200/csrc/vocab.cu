@@ -1,10 +1,11 @@
 // vocab.cu -- vocabulary analyzer of tft.compute_and_apply_vocabulary (reference call site
 // airflow-dags/taxi_utils.py:121-126, top_k=_VOCAB_SIZE :51, num_oov_buckets=_OOV_SIZE :54).
 //
-// Counting: one persistent CTA per SM walks row tiles.  The tile's term bytes are staged into
-// shared memory with coalesced 16-byte loads; every row's term gets a 128-bit identity
+// Counting: one persistent CTA per SM whose 32 warps each walk their own 96-row steps.  A step's
+// offsets and term bytes are landed in the warp's shared-memory stage by the bulk-copy engine
+// (double-buffered per warp, no block-wide barriers); every row's term gets a 128-bit identity
 // (vocab.cuh: the bytes themselves up to 15 bytes, a double hash beyond) and is counted in a
-// per-CTA shared-memory table (4096 slots) after one warp-level aggregation round; terms that do
+// per-CTA shared-memory table (2048 slots) after one warp-level aggregation round; terms that do
 // not fit go straight to the global open-addressing table (32-byte slots, one DRAM sector per
 // probe), into which the front tables are flushed at the end.  Counts are exact.  The
 // first thread to claim a slot copies the term's bytes into an arena, so the table is
@@ -17,15 +18,19 @@
 
 namespace txf {
 
-constexpr int kVcBlock = 512;             // two persistent CTAs per SM: one computes while the other waits at a barrier
-constexpr int kVcSlots = 2048;            // shared-memory front table per CTA: 2048 x 24 B = 48 KB
+constexpr int kVcWarps = 32;
+constexpr int kVcBlock = kVcWarps * 32;   // ONE persistent CTA per SM; its warps run independent pipelines (no block barriers)
+constexpr int kVcSlots = 2048;            // shared-memory front table of the CTA: 2048 x 24 B = 48 KB
 constexpr int kVcProbes = 8;
-constexpr int kVcRowsPerThread = 2;
-constexpr int kVcTileRows = kVcBlock * kVcRowsPerThread;
-constexpr int kVcStageBytes = 24 * 1024;  // per buffer: staged term bytes of one tile (avg 16 B/row -> 16 KB)
-constexpr size_t kVcSmemBytes = kVcSlots * (8 + 8 + 4 + 4) + kVcTileRows * 2 + StrTilePipe::smem_bytes(kVcStageBytes, kVcTileRows);
+constexpr int kVcStepRows = 96;           // rows per warp and step: three per lane
+constexpr int kVcRowsPerLane = kVcStepRows / 32;
+constexpr int kVcOffSlots = 100;          // offsets staged per step: 96 + 1, padded to a multiple of 16 bytes
+constexpr int kVcStageCap = 2304;         // staged term bytes per step (24 B per row on average; longer steps read the pool directly)
+constexpr int kVcStageBytes = 16 + kVcOffSlots * 4 + kVcStageCap;  // header | offsets | bytes
+constexpr int kVcWarpBytes = 2 * kVcStageBytes + kVcStepRows * 2;  // two stages + the warp's long-term queue
+constexpr size_t kVcSmemBytes = kVcSlots * (8 + 8 + 4 + 4) + static_cast<size_t>(kVcWarps) * kVcWarpBytes + kVcWarps * 2 * 8;
 constexpr uint32_t kPadEnt = 0xFFFFFFFFu;
-constexpr int kVcGrid = 2 * kSMs;
+constexpr int kVcGrid = kSMs;
 constexpr uint32_t kVcLocalCodes = kVcGrid * kVcSlots;  // codes below this: (CTA, front-table slot); above: global slot
 
 __device__ __forceinline__ unsigned long long ldcg64(const unsigned long long* p) {
@@ -136,57 +141,100 @@ __device__ __forceinline__ void vc_count(const VcFront& f, bool has, StrKey key,
   if (has && f.codes != nullptr) __stcs(f.codes + row, code);  // the row's term, dictionary-encoded
 }
 
-// One tile: phase A counts the short terms (exact identity, a handful of instructions) and
-// queues the long ones; phase B hashes the queued terms with all lanes busy -- columns that mix
-// empty/short and long terms would otherwise idle most lanes of a warp during the hashing.
+// ---- per-warp pipeline ------------------------------------------------------------------------
+// Every warp of the CTA owns two stages in shared memory and walks its own sequence of 96-row
+// steps: lane 0 asks the bulk-copy engine for the step's offsets and term bytes (cp.async.bulk,
+// completion on the stage's mbarrier), the warp waits on that barrier only, counts, and re-arms the
+// stage for the step after next.  No block-wide barrier exists between the table initialisation and
+// the final flush, so no warp ever waits for another one.
+// Stage layout: [a0: pool offset of byte 0 (8) | staged (4) | meta (4)] [offsets x 100] [bytes].
+struct VcStage {
+  uint8_t* base;  // generic pointer to the stage
+  __device__ __forceinline__ long long& a0() const { return *reinterpret_cast<long long*>(base); }
+  __device__ __forceinline__ int& staged() const { return *reinterpret_cast<int*>(base + 8); }
+  __device__ __forceinline__ int& meta() const { return *reinterpret_cast<int*>(base + 12); }
+  __device__ __forceinline__ int32_t* off() const { return reinterpret_cast<int32_t*>(base + 16); }
+  __device__ __forceinline__ uint8_t* bytes() const { return base + 16 + kVcOffSlots * 4; }
+};
+
+struct VcSource {
+  const int32_t* offsets;
+  const uint8_t* pool;
+  const uint8_t* valid;
+  int64_t n;
+  bool pool_ok, off_ok;  // 16-byte aligned bases (bulk copies need them)
+};
+
+// lane 0 of the owning warp: start the copies of step rows [r0, r1) into the stage
+__device__ __forceinline__ void vc_issue(const VcSource& src, const VcStage& st, uint64_t* bar, int64_t r0, int64_t r1) {
+  const long long b0 = __ldg(src.offsets + r0), e0 = __ldg(src.offsets + r1);
+  const long long start = b0 & ~15LL;
+  const long long need = ((e0 - start + 15) & ~15LL) + 32;  // window loads touch < 24 bytes past a term
+  const bool do_bytes = src.pool_ok && need <= kVcStageCap;
+  const bool do_meta = src.off_ok && (r1 - r0) == kVcStepRows && r0 + kVcOffSlots <= src.n + 1;
+  st.a0() = start;
+  st.staged() = do_bytes;
+  st.meta() = do_meta;
+  const uint32_t total = (do_bytes ? static_cast<uint32_t>(need) : 0u) + (do_meta ? kVcOffSlots * 4u : 0u);
+  if (total == 0) {
+    mbar_arrive(bar);
+    return;
+  }
+  fence_proxy_async();  // the stage was read through ordinary loads until now
+  mbar_arrive_expect_tx(bar, total);
+  if (do_bytes) bulk_copy_g2s(st.bytes(), src.pool + start, static_cast<uint32_t>(need), bar);
+  if (do_meta) bulk_copy_g2s(st.off(), src.offsets + r0, kVcOffSlots * 4u, bar);
+}
+
+// One step of one warp.  Phase A counts the short terms (exact identity, a handful of
+// instructions) and queues the long ones; phase B hashes the queued terms with the lanes packed --
+// columns that mix empty/short and long terms would otherwise idle most lanes during the hashing.
 template <bool STAGED, bool META>
-__device__ __forceinline__ void vc_tile(const VcFront& f, const TileRows<META> rows, const uint8_t* base, int64_t r0, int64_t r1,
-                                        uint16_t* s_queue, uint32_t* s_nq, const uint4* s_mask) {
-  const uint32_t sbase = STAGED ? smem_u32(base + rows.begin(r0)) - static_cast<uint32_t>(rows.begin(r0)) : 0u;
+__device__ __forceinline__ void vc_step(const VcFront& f, const VcSource& src, const VcStage& st, int64_t r0, int64_t r1,
+                                        uint16_t* wqueue, const uint4* s_mask) {
+  const int32_t* soff = st.off();
+  const uint8_t* base = STAGED ? st.bytes() - st.a0() : src.pool;       // the term at pool offset o is at base + o
+  const uint32_t sbase = STAGED ? smem_u32(st.bytes()) - static_cast<uint32_t>(st.a0()) : 0u;
+  uint32_t nq = 0;
 #pragma unroll
-  for (int j = 0; j < kVcRowsPerThread; ++j) {
-    const int64_t row = r0 + j * kVcBlock + threadIdx.x;
-    const bool in_tile = row < r1;
+  for (int j = 0; j < kVcRowsPerLane; ++j) {
+    const int64_t row = r0 + j * 32 + lane_id();
+    const bool in_step = row < r1;
     int32_t b = 0;
     uint32_t len = 0;
-    if (in_tile) {
-      b = rows.begin(row);
-      if (rows.present(row)) len = static_cast<uint32_t>(rows.end(row) - b);
+    if (in_step) {
+      b = META ? soff[row - r0] : __ldg(src.offsets + row);
+      if (row_valid(src.valid, row)) len = static_cast<uint32_t>((META ? soff[row - r0 + 1] : __ldg(src.offsets + row + 1)) - b);
     }
-    const bool is_long = in_tile && len > kExactKeyMax;
+    const bool is_long = in_step && len > kExactKeyMax;
     StrKey key{0, 0};
-    if (in_tile && !is_long)
+    if (in_step && !is_long)
       key = STAGED ? make_key_exact_smem(sbase + static_cast<uint32_t>(b), len, s_mask) : make_key_exact(PtrFetch{base + b}, len);
     const unsigned lm = __ballot_sync(0xffffffffu, is_long);
-    if (lm) {  // queue the long rows of this warp (one shared atomic per warp)
-      uint32_t qb = 0;
-      const int leader = __ffs(lm) - 1;
-      if (static_cast<int>(lane_id()) == leader) qb = atomicAdd(s_nq, static_cast<uint32_t>(__popc(lm)));
-      qb = __shfl_sync(0xffffffffu, qb, leader);
-      if (is_long) s_queue[qb + __popc(lm & ((1u << lane_id()) - 1u))] = static_cast<uint16_t>(row - r0);
-    }
-    vc_count(f, in_tile && !is_long, key, row, b, len);
+    if (is_long) wqueue[nq + __popc(lm & ((1u << lane_id()) - 1u))] = static_cast<uint16_t>(row - r0);
+    nq += __popc(lm);  // warp-uniform
+    vc_count(f, in_step && !is_long, key, row, b, len);
   }
-  __syncthreads();
-  const uint32_t nq = *s_nq;
-  for (uint32_t t0 = 0; t0 < nq; t0 += kVcBlock) {  // block-uniform trip count
-    const uint32_t t = t0 + threadIdx.x;
+  __syncwarp();
+  for (uint32_t t0 = 0; t0 < nq; t0 += 32) {  // warp-uniform trip count
+    const uint32_t t = t0 + lane_id();
     const bool has = t < nq;
     int64_t row = r0;
     int32_t b = 0;
     uint32_t len = 0;
     StrKey key{0, 0};
     if (has) {
-      row = r0 + s_queue[t];
-      b = rows.begin(row);
-      len = static_cast<uint32_t>(rows.end(row) - b);
+      const uint32_t r = wqueue[t];
+      row = r0 + r;
+      b = META ? soff[r] : __ldg(src.offsets + row);
+      len = static_cast<uint32_t>((META ? soff[r + 1] : __ldg(src.offsets + row + 1)) - b);
       key = STAGED ? make_key_hashed_smem(sbase + static_cast<uint32_t>(b), len) : make_key_hashed(PtrFetch{base + b}, len);
     }
     vc_count(f, has, key, row, b, len);
   }
 }
 
-__global__ void __launch_bounds__(kVcBlock, 2) vocab_count_kernel(const int32_t* __restrict__ offsets,
+__global__ void __launch_bounds__(kVcBlock, 1) vocab_count_kernel(const int32_t* __restrict__ offsets,
                                                                   const uint8_t* __restrict__ pool,
                                                                   const uint8_t* __restrict__ valid, int64_t n,
                                                                   CountSlot* table, uint64_t mask, uint8_t* arena,
@@ -194,7 +242,6 @@ __global__ void __launch_bounds__(kVcBlock, 2) vocab_count_kernel(const int32_t*
                                                                   uint32_t* __restrict__ codes,
                                                                   uint32_t* __restrict__ local2global) {
   extern __shared__ __align__(16) uint8_t vc_smem[];
-  __shared__ uint32_t s_nq;
   __shared__ uint4 s_mask[16];
   fill_short_masks(s_mask);
   VcFront f;
@@ -202,38 +249,40 @@ __global__ void __launch_bounds__(kVcBlock, 2) vocab_count_kernel(const int32_t*
   f.s_b = f.s_a + kVcSlots;
   f.s_cnt = reinterpret_cast<uint32_t*>(f.s_b + kVcSlots);
   f.s_row = f.s_cnt + kVcSlots;
-  uint16_t* s_queue = reinterpret_cast<uint16_t*>(f.s_row + kVcSlots);  // [kVcTileRows]
   f.table = table; f.mask = mask; f.arena = arena; f.arena_cap = arena_cap; f.ctrl = ctrl; f.codes = codes; f.pool = pool;
   for (int i = threadIdx.x; i < kVcSlots; i += kVcBlock) { f.s_a[i] = 0; f.s_b[i] = 0; f.s_cnt[i] = 0; f.s_row[i] = 0; }
-  if (threadIdx.x == 0) s_nq = 0;
-  StrTilePipe pipe;
-  pipe.init(reinterpret_cast<uint8_t*>(s_queue + kVcTileRows), kVcStageBytes, kVcTileRows, offsets, pool, valid, n);  // syncs
+  const int warp = threadIdx.x >> 5;
+  uint8_t* wbase = reinterpret_cast<uint8_t*>(f.s_row + kVcSlots) + static_cast<size_t>(warp) * kVcWarpBytes;
+  uint16_t* wqueue = reinterpret_cast<uint16_t*>(wbase + 2 * kVcStageBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(f.s_row + kVcSlots) + static_cast<size_t>(kVcWarps) * kVcWarpBytes) +
+                   2 * warp;
+  VcSource src{offsets, pool, valid, n, (reinterpret_cast<uintptr_t>(pool) & 15) == 0, (reinterpret_cast<uintptr_t>(offsets) & 15) == 0};
+  if (lane_id() == 0) {
+    mbar_init(&bars[0], 1);
+    mbar_init(&bars[1], 1);
+    mbar_fence_init();
+  }
+  __syncthreads();  // table zeroed, barriers initialised: the only block-wide barrier before the flush
 
-  const int64_t ntiles = (n + kVcTileRows - 1) / kVcTileRows;
-  auto tile_end = [&](int64_t t) { return (t + 1) * kVcTileRows < n ? (t + 1) * kVcTileRows : n; };
-  if (threadIdx.x == 0) {  // prologue: the first two tiles of this CTA
-    if (blockIdx.x < ntiles) pipe.issue(blockIdx.x * static_cast<int64_t>(kVcTileRows), tile_end(blockIdx.x), 0);
-    if (blockIdx.x + gridDim.x < ntiles)
-      pipe.issue((blockIdx.x + gridDim.x) * static_cast<int64_t>(kVcTileRows), tile_end(blockIdx.x + gridDim.x), 1);
+  const int64_t nsteps = (n + kVcStepRows - 1) / kVcStepRows;
+  const int64_t gw = static_cast<int64_t>(blockIdx.x) * kVcWarps + warp, nw = static_cast<int64_t>(gridDim.x) * kVcWarps;
+  auto step_end = [&](int64_t t) { return (t + 1) * kVcStepRows < n ? (t + 1) * kVcStepRows : n; };
+  if (lane_id() == 0) {
+    if (gw < nsteps) vc_issue(src, VcStage{wbase}, &bars[0], gw * kVcStepRows, step_end(gw));
+    if (gw + nw < nsteps) vc_issue(src, VcStage{wbase + kVcStageBytes}, &bars[1], (gw + nw) * kVcStepRows, step_end(gw + nw));
   }
   uint32_t k = 0;
-  for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++k) {
-    const int64_t r0 = tile * kVcTileRows;
-    const int64_t r1 = tile_end(tile);
-    const uint8_t* base = pipe.acquire(k & 1, k >> 1);
-    const int bsel = k & 1;
-    if (pipe.staged[bsel] && pipe.meta[bsel])
-      vc_tile<true, true>(f, tile_rows_of<true>(pipe, bsel, r0), base, r0, r1, s_queue, &s_nq, s_mask);
-    else if (pipe.staged[bsel])
-      vc_tile<true, false>(f, tile_rows_of<false>(pipe, bsel, r0), base, r0, r1, s_queue, &s_nq, s_mask);
-    else
-      vc_tile<false, false>(f, tile_rows_of<false>(pipe, bsel, r0), base, r0, r1, s_queue, &s_nq, s_mask);
-    __syncthreads();  // everyone is done with this buffer: refill it with the tile after next
-    const int64_t nxt = tile + 2 * static_cast<int64_t>(gridDim.x);
-    if (threadIdx.x == 0) {
-      s_nq = 0;
-      if (nxt < ntiles) pipe.issue(nxt * kVcTileRows, tile_end(nxt), k & 1);
-    }
+  for (int64_t t = gw; t < nsteps; t += nw, ++k) {
+    const int s = k & 1;
+    const int64_t r0 = t * kVcStepRows, r1 = step_end(t);
+    mbar_wait(&bars[s], (k >> 1) & 1u);
+    const VcStage st{wbase + s * kVcStageBytes};
+    if (st.staged() && st.meta()) vc_step<true, true>(f, src, st, r0, r1, wqueue, s_mask);
+    else if (st.staged()) vc_step<true, false>(f, src, st, r0, r1, wqueue, s_mask);
+    else vc_step<false, false>(f, src, st, r0, r1, wqueue, s_mask);
+    __syncwarp();  // every lane is done with the stage: refill it with the step after next
+    const int64_t nxt = t + 2 * nw;
+    if (lane_id() == 0 && nxt < nsteps) vc_issue(src, st, &bars[s], nxt * kVcStepRows, step_end(nxt));
   }
   __syncthreads();
   for (int i = threadIdx.x; i < kVcSlots; i += kVcBlock) {  // flush the front table
@@ -521,7 +570,7 @@ int txf_vocab_count(const int32_t* offsets_dev, const uint8_t* pool_dev, const u
     TXF_CUDA(cudaMemsetAsync(local2global_dev, 0xFF, static_cast<size_t>(kVcLocalCodes) * sizeof(uint32_t),
                              static_cast<cudaStream_t>(stream)));
   if (n == 0) return TXF_OK;
-  int64_t want = (n + kVcTileRows - 1) / kVcTileRows;
+  int64_t want = (n + static_cast<int64_t>(kVcStepRows) * kVcWarps - 1) / (static_cast<int64_t>(kVcStepRows) * kVcWarps);
   int grid = static_cast<int>(want < kVcGrid ? want : kVcGrid);
   TXF_CUDA(cudaFuncSetAttribute(vocab_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kVcSmemBytes)));
   vocab_count_kernel<<<grid, kVcBlock, kVcSmemBytes, static_cast<cudaStream_t>(stream)>>>(
