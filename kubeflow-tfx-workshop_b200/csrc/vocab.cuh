@@ -12,16 +12,14 @@ namespace txf {
 // tables are keyed by a cheaper 128-bit identity (a, b):
 //   * terms of <= 15 bytes: the bytes themselves (zero padded) with the length in b's top byte --
 //     exact, no hashing at all (payment types, most categorical strings);
-//   * longer terms: two independent 64-bit multiply-rotate hashes of all bytes and the length
-//     (126 effective bits; the top byte of b marks the class so the two classes never meet).
+//   * longer terms: two independent 64-bit multiply-fold hashes of all bytes and the length
+//     (126 bits kept; the top byte of b marks the class so the two classes never meet).
 // a == 0 and b == 0 are reserved for "unclaimed slot": b is never 0 by construction, and a == 0
 // is remapped to 1 with a flag bit in b.
 // ---------------------------------------------------------------------------------------------
 struct StrKey {
   unsigned long long a, b;
 };
-
-__host__ __device__ __forceinline__ uint64_t rotl64(uint64_t v, int s) { return (v << s) | (v >> (64 - s)); }
 
 constexpr uint32_t kExactKeyMax = 15;  // terms up to this length are their own identity
 
@@ -36,19 +34,37 @@ __host__ __device__ __forceinline__ StrKey finish_key(uint64_t k0, uint64_t k1) 
 // Mixing of a long term.  Like FarmHash, terms of 16..32 bytes are covered by four (overlapping)
 // 8-byte windows -- first 16 and last 16 bytes -- so there is no loop, no tail and no masking;
 // 33..64 bytes take eight windows, longer terms a loop over 32-byte blocks plus the last 32 bytes.
+// The mixer is two independent 64-bit lanes of the multiply-fold kind: each lane keeps two 32-bit
+// words, XORs one half of the window into each, and replaces them by the low and high half of
+// their full 32x32->64 product.  That is three instructions per lane and window on the GPU
+// (two 3-input XORs, one wide multiply) where a 64-bit multiply-rotate chain costs about ten.
+// The lanes use different constants, different starting words and opposite halves of the window.
 struct KeyMixer {
-  uint64_t h1, h2;
+  uint32_t a1, b1, a2, b2;
   __host__ __device__ __forceinline__ explicit KeyMixer(uint32_t n)
-      : h1(static_cast<uint64_t>(n) * 0x9E3779B97F4A7C15ULL + 0x7F4A7C159E3779B9ULL),
-        h2((static_cast<uint64_t>(n) ^ 0xD6E8FEB86659FD93ULL) * 0xC2B2AE3D27D4EB4FULL) {}
+      : a1(n * 0x9E3779B1u + 0x7F4A7C15u), b1(n ^ 0x632BE5ABu), a2((n ^ 0xD6E8FEB8u) * 0xC2B2AE3Du), b2(n + 0x27D4EB2Fu) {}
   __host__ __device__ __forceinline__ void add(uint64_t w) {
-    h1 = (rotl64(h1, 27) ^ w) * 0xFF51AFD7ED558CCDULL;
-    h2 = (rotl64(h2, 31) + w) * 0xC4CEB9FE1A85EC53ULL;
+    const uint32_t lo = static_cast<uint32_t>(w), hi = static_cast<uint32_t>(w >> 32);
+    const uint64_t p = static_cast<uint64_t>(a1 ^ lo ^ 0x53C5CA59u) * (b1 ^ hi ^ 0x74743C1Bu);
+    const uint64_t q = static_cast<uint64_t>(a2 ^ hi ^ 0xA0761D65u) * (b2 ^ lo ^ 0xE7037ED1u);
+    a1 = static_cast<uint32_t>(p); b1 = static_cast<uint32_t>(p >> 32);
+    a2 = static_cast<uint32_t>(q); b2 = static_cast<uint32_t>(q >> 32);
   }
   __host__ __device__ __forceinline__ StrKey finish() {
-    h1 ^= h1 >> 32; h1 *= 0x9FB21C651E98DF25ULL; h1 ^= h1 >> 29;
-    h2 ^= h2 >> 31; h2 *= 0xD6E8FEB86659FD93ULL; h2 ^= h2 >> 32;
-    return finish_key(h1, (h2 & 0x3FFFFFFFFFFFFFFFULL) | 0x8000000000000000ULL);  // top byte 0x80..0xBF
+    // two data-free rounds so the words of the last window reach every output bit.  The low half of
+    // a product is its weak half, so the low output word also takes the high half (lo ^ hi) and
+    // the high output word is crossed with the previous round's low word.
+    const uint64_t p = static_cast<uint64_t>(a1 ^ 0x8EBC6AF1u) * (b1 ^ 0x589965CDu);
+    const uint64_t q = static_cast<uint64_t>(a2 ^ 0x1D8E4E27u) * (b2 ^ 0xEB44ACCBu);
+    const uint32_t pl = static_cast<uint32_t>(p), ph = static_cast<uint32_t>(p >> 32);
+    const uint32_t ql = static_cast<uint32_t>(q), qh = static_cast<uint32_t>(q >> 32);
+    const uint64_t r = static_cast<uint64_t>(pl ^ 0x53C5CA59u) * (ph ^ 0x74743C1Bu);
+    const uint64_t t = static_cast<uint64_t>(ql ^ 0xA0761D65u) * (qh ^ 0xE7037ED1u);
+    const uint32_t rl = static_cast<uint32_t>(r), rh = static_cast<uint32_t>(r >> 32);
+    const uint32_t tl = static_cast<uint32_t>(t), th = static_cast<uint32_t>(t >> 32);
+    const uint64_t k0 = static_cast<uint64_t>(rl ^ rh) | (static_cast<uint64_t>(rh ^ pl) << 32);
+    const uint64_t k1 = static_cast<uint64_t>(tl ^ th) | (static_cast<uint64_t>(th ^ ql) << 32);
+    return finish_key(k0, (k1 & 0x3FFFFFFFFFFFFFFFULL) | 0x8000000000000000ULL);  // top byte 0x80..0xBF
   }
 };
 
