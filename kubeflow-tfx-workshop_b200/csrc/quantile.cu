@@ -267,7 +267,7 @@ __global__ void qsample_kernel(NumColsView cols, int64_t n, int64_t M, uint64_t 
 constexpr int kQBlock = 256;
 constexpr int kQLutBits = 12;            // 4096-entry bin table over [first edge, last edge]
 constexpr int kQTileQuads = 2 * kQBlock; // a tile = 2 quads (8 keys) per thread
-constexpr int kQCandBuf = 4096;          // CTA-local candidate buffer (keys); flushed when half full
+constexpr int kQCandBuf = 2048;          // CTA-local candidate buffer (keys); flushed when half full (8 KB: five CTAs per SM)
 
 template <bool F32>
 __device__ __forceinline__ float4 load_quad_as_f32(const void* values, int64_t q) {
@@ -322,14 +322,18 @@ __global__ void __launch_bounds__(kQBlock) qcount_kernel(NumColsView cols, int64
   // private 16-bit counter of (cell, thread): lanes of a warp sit in 32 different banks, warps w
   // and w+4 share the words (low/high half), so the read-modify-write never bank-conflicts
   const int my_slot = (((threadIdx.x >> 5) & 3) * 32 + static_cast<int>(lane_id())) * 2 + (threadIdx.x >> 7);
-  auto visit = [&](uint32_t key) {
+  const uint32_t cnt_addr = smem_addr(s_cnt) + 2u * static_cast<uint32_t>(my_slot);
+  // table entry of a key: number of edges below it (exact unless bit 15 says the bin holds edges)
+  auto lookup = [&](uint32_t key) -> uint32_t {
     const uint32_t d = key - first;  // wraps below the first edge; the table index is clamped, the result overridden
     uint32_t bin = d >> shift;
     bin = bin < (1u << kQLutBits) ? bin : (1u << kQLutBits) - 1;
     uint32_t t = s_lut[bin];
     t = key < first ? 0u : t;
-    t = key > last ? static_cast<uint32_t>(E) : t;
-    int lo = t & 0x7FFF;  // number of edges < key (exact unless the bin holds edges: then refined)
+    return key > last ? static_cast<uint32_t>(E) : t;
+  };
+  auto count = [&](uint32_t key, uint32_t t) {
+    int lo = t & 0x7FFF;
     bool eq = false;
     if (t & 0x8000) {
       uint32_t e = s_edges[lo];
@@ -340,7 +344,10 @@ __global__ void __launch_bounds__(kQBlock) qcount_kernel(NumColsView cols, int64
       eq = lo < E && e == key;
     }
     const int cell = 2 * lo + (eq ? 1 : 0);
-    s_cnt[cell * kQBlock + my_slot] += 1;      // <= 65535 keys per thread per launch (grid sizing)
+    {  // private counter += 1 through explicit shared-window addresses (<= 65535 keys per thread per launch: grid sizing)
+      const uint32_t a = cnt_addr + static_cast<uint32_t>(cell) * (2u * kQBlock);
+      sts_u16(a, lds_u16(a) + 1u);
+    }
     if ((lo & 1) && !eq) {  // strictly inside bracket (lo-1)/2: keep the key
       const uint32_t pos = atomicAdd(&s_ncand, 1u);
       if (pos < kQCandBuf) {
@@ -351,10 +358,14 @@ __global__ void __launch_bounds__(kQBlock) qcount_kernel(NumColsView cols, int64
       }
     }
   };
+  auto visit = [&](uint32_t key) { count(key, lookup(key)); };
+  // the four table lookups of a quad are issued together (independent loads), then the counters
   auto visit_quad = [&](float4 x, uint32_t vbyte, int64_t q) {  // vbyte: raw bitmap byte of the quad (prefetched)
     const uint32_t m = valid == nullptr ? 0xFu : (vbyte >> ((4 * q) & 4)) & 0xFu;
-    visit(f32_key(m & 1 ? x.x : 0.f)); visit(f32_key(m & 2 ? x.y : 0.f));
-    visit(f32_key(m & 4 ? x.z : 0.f)); visit(f32_key(m & 8 ? x.w : 0.f));
+    const uint32_t k0 = f32_key(m & 1 ? x.x : 0.f), k1 = f32_key(m & 2 ? x.y : 0.f), k2 = f32_key(m & 4 ? x.z : 0.f),
+                   k3 = f32_key(m & 8 ? x.w : 0.f);
+    const uint32_t t0 = lookup(k0), t1 = lookup(k1), t2 = lookup(k2), t3 = lookup(k3);
+    count(k0, t0); count(k1, t1); count(k2, t2); count(k3, t3);
   };
   auto flush = [&]() {  // all threads; s_ncand is stable on entry
     if (threadIdx.x == 0) s_base = atomicAdd(&cand_count[c], static_cast<unsigned long long>(s_ncand < kQCandBuf ? s_ncand : kQCandBuf));
