@@ -39,14 +39,33 @@ def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
     return None if t is None else t.data_ptr()
 
 
-@dataclass
 class VocabResult:
-    spec_key: Tuple
-    size: int                      # len(vocabulary) -- the real list length, not top_k
-    lookup: torch.Tensor           # uint8 bytes of the 16-byte-slot lookup table
-    lookup_cap: int
-    terms_offsets: torch.Tensor    # int32 [size+1] (device), id order
-    terms_pool: torch.Tensor       # uint8 (device)
+    """One finished vocabulary.  The term bytes (id order) are exported from the count table only
+    when somebody asks for them (terms(), detach(), save_state): the transform needs the lookup
+    table alone, and the export is a handful of launch-bound kernels."""
+
+    def __init__(self, spec_key: Tuple, size: int, lookup: torch.Tensor, lookup_cap: int, terms_offsets: Optional[torch.Tensor] = None,
+                 terms_pool: Optional[torch.Tensor] = None, export=None):
+        self.spec_key = spec_key
+        self.size = size                      # len(vocabulary) -- the real list length, not top_k
+        self.lookup = lookup                  # uint8 bytes of the 24-byte-slot lookup table
+        self.lookup_cap = lookup_cap
+        self._offsets, self._pool, self._export = terms_offsets, terms_pool, export
+
+    def _materialize(self):
+        if self._offsets is None:
+            self._offsets, self._pool = self._export()
+            self._export = None
+
+    @property
+    def terms_offsets(self) -> torch.Tensor:  # int32 [size+1] (device), id order
+        self._materialize()
+        return self._offsets
+
+    @property
+    def terms_pool(self) -> torch.Tensor:     # uint8 (device)
+        self._materialize()
+        return self._pool
 
     def terms(self) -> List[bytes]:
         o = self.terms_offsets.cpu().numpy()
@@ -740,8 +759,12 @@ class Engine:
         if k == 0:
             return self._vocab_from_terms(vk, [EMPTY_VOCAB_SENTINEL], lookup, lookup_cap)
         nat.call("txf_vocab_build_lookup", table.data_ptr(), sel.data_ptr(), k, lookup.data_ptr(), lookup_cap, s)
-        _, _, _, offsets, pool = self._export_entries(pend, sel, k)
-        return VocabResult(vk, k, lookup, lookup_cap, offsets.to(torch.int32), pool)
+
+        def export():  # valid until the next analyze() on this Engine overwrites the count table (like the rest of the state)
+            _, _, _, offsets, pool = self._export_entries(pend, sel, k)
+            return offsets.to(torch.int32), pool
+
+        return VocabResult(vk, k, lookup, lookup_cap, export=export)
 
     def _vocab_from_terms(self, vk: Tuple, terms: List[bytes], lookup: Optional[torch.Tensor] = None,
                           lookup_cap: Optional[int] = None) -> VocabResult:
