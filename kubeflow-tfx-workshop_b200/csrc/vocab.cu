@@ -116,7 +116,7 @@ __device__ __noinline__ int vc_find_slow(unsigned long long* s_a, unsigned long 
 
 // Count one term per lane (has == false: the lane only takes part in the warp votes).  Must be
 // called by all 32 lanes of a warp together.
-__device__ __forceinline__ void vc_count(const VcFront& f, bool has, StrKey key, int64_t row, int32_t b, uint32_t len) {
+__device__ __forceinline__ int vc_count(const VcFront& f, bool has, StrKey key, int64_t row, int32_t b, uint32_t len) {
   int slot = -1;
   if (has) {
     const uint32_t idx = static_cast<uint32_t>(home_slot(key.a, key.b, kVcSlots - 1));
@@ -139,6 +139,7 @@ __device__ __forceinline__ void vc_count(const VcFront& f, bool has, StrKey key,
   if (has && slot < 0)  // front table full around this term: count it in the global table
     code = kVcLocalCodes + table_add(f.table, f.mask, key.a, key.b, 1ULL, f.pool + b, len, f.arena, f.arena_cap, f.ctrl);
   if (has && f.codes != nullptr) __stcs(f.codes + row, code);  // the row's term, dictionary-encoded
+  return slot;
 }
 
 // ---- per-warp pipeline ------------------------------------------------------------------------
@@ -191,7 +192,7 @@ __device__ __forceinline__ void vc_issue(const VcSource& src, const VcStage& st,
 // columns that mix empty/short and long terms would otherwise idle most lanes during the hashing.
 template <bool STAGED, bool META>
 __device__ __forceinline__ void vc_step(const VcFront& f, const VcSource& src, const VcStage& st, int64_t r0, int64_t r1,
-                                        uint16_t* wqueue, const uint4* s_mask) {
+                                        uint16_t* wqueue, const uint4* s_mask, int& empty_slot) {
   const int32_t* soff = st.off();
   const uint8_t* base = STAGED ? st.bytes() - st.a0() : src.pool;       // the term at pool offset o is at base + o
   const uint32_t sbase = STAGED ? smem_u32(st.bytes()) - static_cast<uint32_t>(st.a0()) : 0u;
@@ -207,13 +208,27 @@ __device__ __forceinline__ void vc_step(const VcFront& f, const VcSource& src, c
       if (row_valid(src.valid, row)) len = static_cast<uint32_t>((META ? soff[row - r0 + 1] : __ldg(src.offsets + row + 1)) - b);
     }
     const bool is_long = in_step && len > kExactKeyMax;
-    StrKey key{0, 0};
-    if (in_step && !is_long)
-      key = STAGED ? make_key_exact_smem(sbase + static_cast<uint32_t>(b), len, s_mask) : make_key_exact(PtrFetch{base + b}, len);
     const unsigned lm = __ballot_sync(0xffffffffu, is_long);
     if (is_long) wqueue[nq + __popc(lm & ((1u << lane_id()) - 1u))] = static_cast<uint16_t>(row - r0);
     nq += __popc(lm);  // warp-uniform
-    vc_count(f, in_step && !is_long, key, row, b, len);
+    // Missing cells are the empty term.  Once the warp knows that term's slot, a row group whose
+    // short terms are all empty (every group of a column like `company`) needs no table search.
+    const bool is_short = in_step && !is_long;
+    const unsigned other = __ballot_sync(0xffffffffu, is_short && len != 0);
+    if (other == 0 && empty_slot >= 0) {
+      const unsigned em = __ballot_sync(0xffffffffu, is_short);
+      if (em) {
+        if (static_cast<int>(lane_id()) == __ffs(em) - 1) atomicAdd(&f.s_cnt[empty_slot], static_cast<uint32_t>(__popc(em)));
+        if (is_short && f.codes != nullptr) __stcs(f.codes + row, blockIdx.x * static_cast<uint32_t>(kVcSlots) + static_cast<uint32_t>(empty_slot));
+      }
+    } else {
+      StrKey key{0, 0};
+      if (is_short)
+        key = STAGED ? make_key_exact_smem(sbase + static_cast<uint32_t>(b), len, s_mask) : make_key_exact(PtrFetch{base + b}, len);
+      const int slot = vc_count(f, is_short, key, row, b, len);
+      const unsigned found = __ballot_sync(0xffffffffu, is_short && len == 0 && slot >= 0);
+      if (found) empty_slot = __shfl_sync(0xffffffffu, slot, __ffs(found) - 1);
+    }
   }
   __syncwarp();
   for (uint32_t t0 = 0; t0 < nq; t0 += 32) {  // warp-uniform trip count
@@ -272,14 +287,15 @@ __global__ void __launch_bounds__(kVcBlock, 1) vocab_count_kernel(const int32_t*
     if (gw + nw < nsteps) vc_issue(src, VcStage{wbase + kVcStageBytes}, &bars[1], (gw + nw) * kVcStepRows, step_end(gw + nw));
   }
   uint32_t k = 0;
+  int empty_slot = -1;  // front-table slot of the empty term once this warp has met it (warp-uniform)
   for (int64_t t = gw; t < nsteps; t += nw, ++k) {
     const int s = k & 1;
     const int64_t r0 = t * kVcStepRows, r1 = step_end(t);
     mbar_wait(&bars[s], (k >> 1) & 1u);
     const VcStage st{wbase + s * kVcStageBytes};
-    if (st.staged() && st.meta()) vc_step<true, true>(f, src, st, r0, r1, wqueue, s_mask);
-    else if (st.staged()) vc_step<true, false>(f, src, st, r0, r1, wqueue, s_mask);
-    else vc_step<false, false>(f, src, st, r0, r1, wqueue, s_mask);
+    if (st.staged() && st.meta()) vc_step<true, true>(f, src, st, r0, r1, wqueue, s_mask, empty_slot);
+    else if (st.staged()) vc_step<true, false>(f, src, st, r0, r1, wqueue, s_mask, empty_slot);
+    else vc_step<false, false>(f, src, st, r0, r1, wqueue, s_mask, empty_slot);
     __syncwarp();  // every lane is done with the stage: refill it with the step after next
     const int64_t nxt = t + 2 * nw;
     if (lane_id() == 0 && nxt < nsteps) vc_issue(src, st, &bars[s], nxt * kVcStepRows, step_end(nxt));
