@@ -178,6 +178,7 @@ class Engine:
         self._static_vocabs: Dict[str, VocabResult] = {}   # StaticVocabSpec.out_key -> lookup built from its terms
         self._formatted: Dict[Tuple, Tuple[Table, StringColumn]] = {}  # (id(table), feature) -> tf.as_string column
         self._consts: Dict[float, torch.Tensor] = {}
+        self._host_consts: Dict[Tuple, torch.Tensor] = {}
         self.bucket_groups: Dict[int, List[str]] = {}
         for s in plan.of(BucketSpec):
             keys = self.bucket_groups.setdefault(s.num_buckets, [])
@@ -202,6 +203,19 @@ class Engine:
             self._ws[key] = t
         elif zero:
             t.zero_()
+        return t
+
+    def _host_const(self, data, dtype) -> torch.Tensor:
+        """Small device tensor with host-computed contents, cached by value.  torch.tensor(...,
+        device=cuda) synchronises the current stream; inside the analyze pass that would stall the
+        host behind every kernel queued so far, so these constants are built once and reused."""
+        key = (dtype, repr(data))
+        t = self._host_consts.get(key)
+        if t is None:
+            if len(self._host_consts) > 256:
+                self._host_consts.clear()
+            t = torch.tensor(data, dtype=dtype, device=self.device)
+            self._host_consts[key] = t
         return t
 
     def _tick(self, name: str):
@@ -273,15 +287,21 @@ class Engine:
             self._analyze_minmax(chunks, state)
             pending_q = {nb: self._quantiles_launch(nb, keys, chunks, n_locals) for nb, keys in self.bucket_groups.items()}
             pending_v = {vk: self._vocab_count(vk, spec, chunks) for vk, spec in self.vocab_specs.items()}
-        # one host round trip: everything queued above has to finish before sizes/flags are read
-        main.synchronize()
-        self._tick("local_pass")
-        if self.comm.active:
-            if self.fixed_exchange:
-                self._exchange_fixed(pending_q, pending_v)
-            else:
-                self._exchange(pending_q, pending_v)
-            self._tick("exchange")
+        if self.comm.active and self.fixed_exchange and not self._profile:
+            # the fixed-layout exchange needs no value from the host: queue it behind the local pass
+            # so that its launches are issued while the GPU is still busy, then wait once
+            self._exchange_fixed(pending_q, pending_v)
+            main.synchronize()
+        else:
+            # one host round trip: everything queued above has to finish before sizes/flags are read
+            main.synchronize()
+            self._tick("local_pass")
+            if self.comm.active:
+                if self.fixed_exchange:
+                    self._exchange_fixed(pending_q, pending_v)
+                else:
+                    self._exchange(pending_q, pending_v)
+                self._tick("exchange")
         for nb, pend in pending_q.items():
             state.buckets[nb] = self._quantiles_finish(nb, pend, chunks, n_total)
         self._tick("quantiles_finish")
@@ -440,7 +460,7 @@ class Engine:
         sample = sample.contiguous()
         M_sum = sample.shape[1]
         # (2) bracket edges = exact order statistics of the sample
-        er = torch.tensor([edges_ranks] * ncols, dtype=torch.int64, device=self.device)
+        er = self._host_const([edges_ranks] * ncols, torch.int64)
         sptrs = nat.ptr_array([sample[c].data_ptr() for c in range(ncols)])
 
         def sample_pass(st, p):
@@ -472,7 +492,7 @@ class Engine:
         keys, T = pend["keys"], pend["T"]
         ncols = len(keys)
         s = self._stream()
-        ranks_dev = torch.tensor(pend["ranks"], dtype=torch.int64, device=self.device)
+        ranks_dev = self._host_const(pend["ranks"], torch.int64)
         direct = self._buf(f"q{nb}_direct", (ncols, T), torch.int32)
         cand_rank = self._buf(f"q{nb}_cand_rank", (ncols, T), torch.int64)
         status = self._buf(f"q{nb}_status", (ncols,), torch.int32)
@@ -619,7 +639,7 @@ class Engine:
         ncols = len(keys)
         s = self._stream()
         ranks = self._target_ranks(n_total, nb)
-        rd = torch.tensor([ranks] * ncols, dtype=torch.int64, device=self.device)
+        rd = self._host_const([ranks] * ncols, torch.int64)
         args = [self._num_args([ch[k] for k in keys]) + (len(ch),) for ch in chunks if len(ch)]
 
         def data_pass(st, p):
