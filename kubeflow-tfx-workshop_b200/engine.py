@@ -253,19 +253,11 @@ class Engine:
         if self._profile:
             torch.cuda.synchronize(self.device)
             self._t0 = time.perf_counter()
-        if self.comm.active:
-            nl = torch.tensor([n_local], dtype=torch.int64, device=self.device)
-            n_locals = [int(v) for v in self.comm.all_gather(nl).flatten().tolist()]
-        else:
-            n_locals = [n_local]
-        n_total = sum(n_locals)
-        self._tick("row_counts")
-        state = TransformState(plan=self.plan, moment_keys=list(self.moment_keys), mean_var=None, moments=None, num_rows=n_total)
+        main = torch.cuda.current_stream()
         self._formatted.clear()
-
         # the three analyzer families are independent: queue them on three streams so that the
         # HBM-bound moments pass and the issue-bound counting passes share the SMs
-        main = torch.cuda.current_stream()
+        pending_v = None
         if self.overlap_streams:
             if self._side is None:
                 self._side = (torch.cuda.Stream(device=self.device), torch.cuda.Stream(device=self.device))
@@ -274,8 +266,19 @@ class Engine:
             start.record(main)
             sv.wait_event(start)
             sq.wait_event(start)
+            # the vocabulary counts need nothing from the other ranks: they are queued before the
+            # row counts are gathered, so the GPU is already busy while the host waits for those
             with torch.cuda.stream(sv):
                 pending_v = {vk: self._vocab_count(vk, spec, chunks) for vk, spec in self.vocab_specs.items()}
+        if self.comm.active:
+            nl = torch.tensor([n_local], dtype=torch.int64, device=self.device)
+            n_locals = [int(v) for v in self.comm.all_gather(nl).flatten().tolist()]
+        else:
+            n_locals = [n_local]
+        n_total = sum(n_locals)
+        self._tick("row_counts")
+        state = TransformState(plan=self.plan, moment_keys=list(self.moment_keys), mean_var=None, moments=None, num_rows=n_total)
+        if self.overlap_streams:
             with torch.cuda.stream(sq):
                 pending_q = {nb: self._quantiles_launch(nb, keys, chunks, n_locals) for nb, keys in self.bucket_groups.items()}
             self._analyze_moments(chunks, state)
