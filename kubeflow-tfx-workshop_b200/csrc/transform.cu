@@ -412,6 +412,143 @@ __global__ void __launch_bounds__(kXfBlock, 1) transform_kernel(const __grid_con
   }
 }
 
+// ---- numeric ops as one grid of (op, tile) blocks ----------------------------------------------
+// Measured on this GPU (tools/probes/copy_probe.cu): a plain int64 copy runs at 6.6-6.7 TB/s as a
+// one-shot grid of 256-thread blocks, 64 bytes in flight per thread, and at 5.8 TB/s as 148
+// persistent 1024-thread blocks walking tiles round-robin -- the hardware block scheduler balances
+// the SMs and the DRAM channels better than a static assignment.  So every op of the program that
+// is not a string lookup runs as ONE launch whose blocks are (op, tile) pairs in op-major order:
+// block b belongs to the op whose tile range contains b; at any moment the running blocks stream
+// through one or two columns.  A tile is 256 threads x 64 bytes of input cells.
+constexpr int kTileThreads = 256;
+constexpr int kTileQuads4 = kTileThreads * 4;  // 4-byte cells: 4 quads of 16 bytes per thread
+constexpr int kTileQuads8 = kTileThreads * 2;  // 8-byte cells: 2 quads of 32 bytes per thread
+
+struct TileProgram {
+  XfProgram prog;
+  int64_t first_block[TXF_MAX_OPS + 1];  // op o owns blocks [first_block[o], first_block[o + 1])
+};
+
+__device__ __forceinline__ bool op_in8(const XfOp& op) {
+  return op.kind == TXF_OP_FILL_I64 || ((op.kind == TXF_OP_ZSCORE || op.kind == TXF_OP_BUCKETIZE) && op.in_dtype == TXF_I64);
+}
+
+__global__ void __launch_bounds__(kTileThreads) transform_tiles_kernel(const __grid_constant__ TileProgram tp, int64_t n) {
+  __shared__ float s_bounds[kLinearBuckets];
+  const int nops = tp.prog.nops;
+  int o = 0;
+  while (o + 1 < nops && static_cast<int64_t>(blockIdx.x) >= tp.first_block[o + 1]) ++o;  // block-uniform, <= 32 steps
+  const XfOp& op = tp.prog.ops[o];
+  const int64_t tile = static_cast<int64_t>(blockIdx.x) - tp.first_block[o];
+  const int kind = op.kind;
+  const int64_t nquads = n >> 2;
+  NumParams p{};
+  if (kind == TXF_OP_ZSCORE) p.z = make_zscale(static_cast<const float*>(op.p0));
+  if (kind == TXF_OP_RATIO_LABEL) p.ratio = op.f0;
+  if (kind == TXF_OP_FILL_STR) p.base = __ldg(static_cast<const int32_t*>(op.in0));
+  if (kind == TXF_OP_BUCKETIZE) {
+    p.nb = *static_cast<const int32_t*>(op.p1);
+    p.b = static_cast<const float*>(op.p0);
+    if (p.nb <= kLinearBuckets) {  // the few boundaries of the linear count: one shared copy per block
+      if (static_cast<int>(threadIdx.x) < p.nb) s_bounds[threadIdx.x] = p.b[threadIdx.x];
+      __syncthreads();
+      p.b = s_bounds;
+    }
+  }
+  void* out = op.out;
+  if (!op_in8(op)) {
+    const float* __restrict__ v = static_cast<const float*>(op.in0);
+    const uint8_t* __restrict__ valid = (kind == TXF_OP_FILL_STR || kind == TXF_OP_VOCAB_CODED) ? nullptr : op.valid0;
+    const int64_t q0 = tile * kTileQuads4 + threadIdx.x;
+    float4 raw[4];
+    uint32_t m[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int64_t q = q0 + u * kTileThreads;
+      raw[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      m[u] = 0;
+      if (q < nquads) { raw[u] = ldg_f4(v + 4 * q); m[u] = quad_valid(valid, 4 * q); }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int64_t q = q0 + u * kTileThreads;
+      if (q >= nquads) continue;
+      const float4 x = fill_f4(raw[u], m[u]);
+      switch (kind) {
+        case TXF_OP_ZSCORE:
+          stcs_f4(static_cast<float*>(out) + 4 * q, make_float4(zscore1(x.x, p.z), zscore1(x.y, p.z), zscore1(x.z, p.z), zscore1(x.w, p.z)));
+          break;
+        case TXF_OP_FILL_F32:
+          stcs_f4(static_cast<float*>(out) + 4 * q, x);
+          break;
+        case TXF_OP_FILL_STR:
+          stcs_i4(static_cast<int32_t*>(out) + 4 * q, make_int4(__float_as_int(raw[u].x) - p.base, __float_as_int(raw[u].y) - p.base,
+                                                                 __float_as_int(raw[u].z) - p.base, __float_as_int(raw[u].w) - p.base));
+          break;
+        case TXF_OP_BUCKETIZE: {
+          long long id[4];
+          bucket_quad(x, p, id);
+          store_i64x4(static_cast<long long*>(out), 4 * q, id[0], id[1], id[2], id[3]);
+          break;
+        }
+        case TXF_OP_VOCAB_CODED: {  // dictionary decode: codes written by the count pass -> final ids
+          const long long* __restrict__ tab = static_cast<const long long*>(op.p0);
+          store_i64x4(static_cast<long long*>(out), 4 * q, __ldg(tab + __float_as_uint(raw[u].x)), __ldg(tab + __float_as_uint(raw[u].y)),
+                      __ldg(tab + __float_as_uint(raw[u].z)), __ldg(tab + __float_as_uint(raw[u].w)));
+          break;
+        }
+        default: {  // TXF_OP_RATIO_LABEL: second fp32 column (tips)
+          const float4 t = fill_f4(ldg_f4(static_cast<const float*>(op.in1) + 4 * q), quad_valid(op.valid1, 4 * q));
+          store_i64x4(static_cast<long long*>(out), 4 * q, label1(x.x, t.x, p.ratio), label1(x.y, t.y, p.ratio), label1(x.z, t.z, p.ratio),
+                      label1(x.w, t.w, p.ratio));
+          break;
+        }
+      }
+    }
+    // offsets columns have n + 1 entries: entry 4 * nquads is written here, the rest of the tail below
+    if (kind == TXF_OP_FILL_STR && tile == 0 && threadIdx.x == 0) {
+      const int32_t* off = static_cast<const int32_t*>(op.in0);
+      static_cast<int32_t*>(out)[4 * nquads] = off[4 * nquads] - p.base;
+    }
+  } else {
+    const long long* __restrict__ v = static_cast<const long long*>(op.in0);
+    const uint8_t* __restrict__ valid = op.valid0;
+    const int64_t q0 = tile * kTileQuads8 + threadIdx.x;
+    longlong2 ra[2], rb[2];
+    uint32_t m[2];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const int64_t q = q0 + u * kTileThreads;
+      ra[u] = make_longlong2(0, 0); rb[u] = make_longlong2(0, 0); m[u] = 0;
+      if (q < nquads) { ra[u] = ldg_l2(v + 4 * q); rb[u] = ldg_l2(v + 4 * q + 2); m[u] = quad_valid(valid, 4 * q); }
+    }
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const int64_t q = q0 + u * kTileThreads;
+      if (q >= nquads) continue;
+      const long long a = m[u] & 1 ? ra[u].x : 0LL, b = m[u] & 2 ? ra[u].y : 0LL, c = m[u] & 4 ? rb[u].x : 0LL,
+                      d = m[u] & 8 ? rb[u].y : 0LL;
+      switch (kind) {
+        case TXF_OP_FILL_I64:
+          store_i64x4(static_cast<long long*>(out), 4 * q, a, b, c, d);
+          break;
+        case TXF_OP_ZSCORE:
+          stcs_f4(static_cast<float*>(out) + 4 * q, make_float4(zscore1(i64_to_f32(a), p.z), zscore1(i64_to_f32(b), p.z),
+                                                                zscore1(i64_to_f32(c), p.z), zscore1(i64_to_f32(d), p.z)));
+          break;
+        default: {  // TXF_OP_BUCKETIZE
+          long long id[4];
+          bucket_quad(make_float4(i64_to_f32(a), i64_to_f32(b), i64_to_f32(c), i64_to_f32(d)), p, id);
+          store_i64x4(static_cast<long long*>(out), 4 * q, id[0], id[1], id[2], id[3]);
+          break;
+        }
+      }
+    }
+  }
+  // ---- rows past the last full quad (at most 3): the op's first block takes them ----------------
+  if (tile == 0 && threadIdx.x < (n & 3)) op_row(op, nullptr, (nquads << 2) + threadIdx.x, n);
+}
+
 static int g_last_grid = 0, g_last_block = 0, g_last_smem = 0;
 
 }  // namespace txf
@@ -445,8 +582,6 @@ int txf_transform(const txf_op* ops, int nops, int64_t n, txf_stream_t stream) {
       case TXF_OP_BUCKETIZE: {
         TXF_REQUIRE(s.p0 != nullptr && s.p1 != nullptr && s.a0 >= 0, "transform: op %d (bucketize) needs boundaries, count and capacity a0", o);
         TXF_REQUIRE(s.in_dtype == TXF_F32 || s.in_dtype == TXF_I64, "transform: op %d bad dtype", o);
-        int need = static_cast<int>((s.a0 * 4 + 15) & ~15LL);
-        if (smem + need <= kXfSmemBudget) { d.smem_off = smem; smem += need; }
         break;
       }
       case TXF_OP_VOCAB: {
@@ -470,15 +605,50 @@ int txf_transform(const txf_op* ops, int nops, int64_t n, txf_stream_t stream) {
         TXF_REQUIRE(false, "transform: op %d has unknown kind %d", o, s.kind);
     }
   }
-  prog.smem_bytes = smem;
-  if (smem > 48 * 1024)
-    TXF_CUDA(cudaFuncSetAttribute(transform_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-  int64_t ntiles = (n + kXfTileRows - 1) / kXfTileRows;
-  int grid = static_cast<int>(ntiles < kSMs ? ntiles : kSMs);
-  transform_kernel<<<grid, kXfBlock, smem, static_cast<cudaStream_t>(stream)>>>(prog, n);
-  TXF_LAUNCH_CHECK();
-  count_launch(1);
-  g_last_grid = grid; g_last_block = kXfBlock; g_last_smem = smem;
+  // ---- numeric ops: one grid of (op, tile) blocks ------------------------------------------
+  cudaStream_t cs = static_cast<cudaStream_t>(stream);
+  const int64_t nquads = n >> 2;
+  TileProgram tp{};
+  XfProgram vprog{};
+  int64_t blocks = 0;
+  for (int o = 0; o < nops; ++o) {
+    const XfOp& d = prog.ops[o];
+    if (d.kind == TXF_OP_VOCAB) {
+      vprog.ops[vprog.nops++] = d;
+      continue;
+    }
+    XfOp& t = tp.prog.ops[tp.prog.nops];
+    t = d;
+    t.smem_off = -1;  // boundaries are read from p0 (the kernel keeps a per-block copy)
+    const bool in8 = d.kind == TXF_OP_FILL_I64 || ((d.kind == TXF_OP_ZSCORE || d.kind == TXF_OP_BUCKETIZE) && d.in_dtype == TXF_I64);
+    const int64_t tq = in8 ? kTileQuads8 : kTileQuads4;
+    int64_t tiles = (nquads + tq - 1) / tq;
+    if (tiles < 1) tiles = 1;  // the op's first block also takes the rows past the last full quad
+    tp.first_block[tp.prog.nops] = blocks;
+    blocks += tiles;
+    ++tp.prog.nops;
+  }
+  tp.first_block[tp.prog.nops] = blocks;
+  if (tp.prog.nops) {
+    TXF_REQUIRE(blocks < (1LL << 31), "transform: too many tiles");
+    transform_tiles_kernel<<<static_cast<unsigned>(blocks), kTileThreads, 0, cs>>>(tp, n);
+    TXF_LAUNCH_CHECK();
+    count_launch(1);
+    g_last_grid = static_cast<int>(blocks); g_last_block = kTileThreads; g_last_smem = 0;
+  }
+  // ---- string-lookup ops: the persistent kernel with the staged string tiles -------------------
+  if (vprog.nops) {
+    vprog.smem_bytes = smem;
+    vprog.stage_off = 0;
+    if (smem > 48 * 1024)
+      TXF_CUDA(cudaFuncSetAttribute(transform_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    int64_t ntiles = (n + kXfTileRows - 1) / kXfTileRows;
+    int grid = static_cast<int>(ntiles < kSMs ? ntiles : kSMs);
+    transform_kernel<<<grid, kXfBlock, smem, cs>>>(vprog, n);
+    TXF_LAUNCH_CHECK();
+    count_launch(1);
+    if (!tp.prog.nops) { g_last_grid = grid; g_last_block = kXfBlock; g_last_smem = smem; }
+  }
   return TXF_OK;
 }
 
