@@ -1,14 +1,16 @@
 // transform.cu -- the fused per-row phase of preprocessing_fn (reference:
-// airflow-dags/taxi_utils.py:115-145).  ONE persistent kernel (one CTA per SM) runs the whole
-// program of column ops: fill-missing (:86-103), z-score (:116-119), vocabulary lookup with OOV
-// hashing (:121-126), bucketize (:128-130), categorical pass-through (:132-133) and the tips
-// label (:135-143).  The program is walked op-major: all SMs stream the same input column and
-// the same output column at any moment (two sequential DRAM streams instead of 35 interleaved
-// ones), and no grid-wide barrier separates the ops.
+// airflow-dags/taxi_utils.py:115-145): fill-missing (:86-103), z-score (:116-119), vocabulary
+// ids (:121-126), bucketize (:128-130), categorical pass-through (:132-133) and the tips label
+// (:135-143) as ONE program of column ops.
+//
+// All ops except string lookups run as ONE launch whose blocks are (op, tile) pairs in op-major
+// order (transform_tiles_kernel): at any moment the running blocks stream one or two input
+// columns and one or two output columns, and the hardware block scheduler balances SMs and DRAM
+// channels.  String lookups (a vocabulary applied to a table that was not analyzed) run in a
+// second, persistent kernel with the term bytes staged by the bulk-copy engine.
 //
 // Memory-bound by construction: every input cell is read once with 16-byte loads, every output
-// written once with 16-byte streaming stores; the small read-mostly state (bucket boundaries,
-// vocabulary lookup tables) is staged in shared memory once per CTA.
+// written once with 16-byte streaming stores.
 // Algorithmic bytes per row (taxi schema): read 98.1 + Lp + Lc, write 120; the
 // label re-reads `fare` (4 B/row) because ops run column by column.
 #include "vocab.cuh"
@@ -17,8 +19,6 @@
 namespace txf {
 
 constexpr int kXfBlock = 1024;
-constexpr int kXfUnroll = 4;                                   // quads in flight per thread and op
-constexpr int64_t kXfTileRows = 4LL * kXfBlock * kXfUnroll;    // 16384 rows per tile
 constexpr int kXfStageBytes = 48 * 1024;                       // per buffer: staged term bytes of one vocabulary tile
 constexpr int kXfPipeBytes = (StrTilePipe::smem_bytes(kXfStageBytes, 2 * kXfBlock) + 15) & ~15;
 constexpr int kXfVocabTileRows = 2 * kXfBlock;
@@ -167,18 +167,6 @@ __device__ __forceinline__ void store_i64x4(long long* out, int64_t r, long long
   stcs_l2(out + r + 2, make_longlong2(c, d));
 }
 
-// ---- op bodies.  Three loop nests only -- 4-byte inputs, 8-byte inputs, strings -- with the
-// op-specific arithmetic selected by a CTA-uniform switch INSIDE the loop.  (One loop nest per
-// op kind, inlined or called, made ptxas keep the loaded quads in local memory.)
-// A tile is kXfBlock * kXfUnroll quads; tiles are dealt round-robin to CTAs; thread t owns quads
-// q0 + t + j*kXfBlock of a tile.  4-byte inputs keep 4 quads (64 B) in flight per thread, 8-byte
-// inputs 2 quads (64 B).
-#define TXF_FOR_EACH_TILE(nquads_)                                                                  \
-  for (int64_t q0 = static_cast<int64_t>(blockIdx.x) * (kXfBlock * kXfUnroll) + threadIdx.x,        \
-               qstep = static_cast<int64_t>(gridDim.x) * (kXfBlock * kXfUnroll),                     \
-               qtile = static_cast<int64_t>(blockIdx.x) * (kXfBlock * kXfUnroll);                    \
-       qtile < (nquads_); q0 += qstep, qtile += qstep)
-
 __device__ __forceinline__ float4 fill_f4(float4 r, uint32_t m) {
   return make_float4(m & 1 ? r.x : 0.f, m & 2 ? r.y : 0.f, m & 4 ? r.z : 0.f, m & 8 ? r.w : 0.f);
 }
@@ -204,129 +192,6 @@ __device__ __forceinline__ void bucket_quad(float4 x, const NumParams& p, long l
   }
   id[0] = c0; id[1] = c1; id[2] = c2; id[3] = c3;
 }
-__device__ __forceinline__ NumParams make_params(const XfOp& op, const uint8_t* smem) {
-  NumParams p{};
-  if (op.kind == TXF_OP_ZSCORE) p.z = make_zscale(static_cast<const float*>(op.p0));
-  if (op.kind == TXF_OP_BUCKETIZE) {
-    p.b = op.smem_off >= 0 ? reinterpret_cast<const float*>(smem + op.smem_off) : static_cast<const float*>(op.p0);
-    p.nb = *static_cast<const int32_t*>(op.p1);
-  }
-  if (op.kind == TXF_OP_RATIO_LABEL) p.ratio = op.f0;
-  if (op.kind == TXF_OP_FILL_STR) p.base = __ldg(static_cast<const int32_t*>(op.in0));
-  return p;
-}
-
-// ops whose input cells are 4 bytes: fp32 z-score / bucketize / fill / label, string offsets
-__device__ __forceinline__ void run_in4(const XfOp& op, const uint8_t* smem, int64_t nquads) {
-  const NumParams p = make_params(op, smem);
-  const int kind = op.kind;
-  const float* __restrict__ v = static_cast<const float*>(op.in0);
-  const float* __restrict__ v1 = static_cast<const float*>(op.in1);
-  const uint8_t* __restrict__ valid = (kind == TXF_OP_FILL_STR || kind == TXF_OP_VOCAB_CODED) ? nullptr : op.valid0;
-  const uint8_t* __restrict__ valid1 = op.valid1;
-  void* out = op.out;
-  TXF_FOR_EACH_TILE(nquads) {
-    float4 raw[4];
-    uint32_t m[4];
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      int64_t q = q0 + static_cast<int64_t>(u) * kXfBlock;
-      raw[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-      m[u] = 0;
-      if (q < nquads) { raw[u] = ldg_f4(v + 4 * q); m[u] = quad_valid(valid, 4 * q); }
-    }
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      int64_t q = q0 + static_cast<int64_t>(u) * kXfBlock;
-      if (q >= nquads) continue;
-      const float4 x = fill_f4(raw[u], m[u]);
-      switch (kind) {
-        case TXF_OP_ZSCORE:
-          stcs_f4(static_cast<float*>(out) + 4 * q, make_float4(zscore1(x.x, p.z), zscore1(x.y, p.z), zscore1(x.z, p.z), zscore1(x.w, p.z)));
-          break;
-        case TXF_OP_FILL_F32:
-          stcs_f4(static_cast<float*>(out) + 4 * q, x);
-          break;
-        case TXF_OP_FILL_STR: {
-          int4 o = make_int4(__float_as_int(raw[u].x) - p.base, __float_as_int(raw[u].y) - p.base, __float_as_int(raw[u].z) - p.base,
-                             __float_as_int(raw[u].w) - p.base);
-          stcs_i4(static_cast<int32_t*>(out) + 4 * q, o);
-          break;
-        }
-        case TXF_OP_BUCKETIZE:
-        {
-          long long id[4];
-          bucket_quad(x, p, id);
-          store_i64x4(static_cast<long long*>(out), 4 * q, id[0], id[1], id[2], id[3]);
-        }
-          break;
-        case TXF_OP_VOCAB_CODED: {  // dictionary decode: codes written by the count pass -> final ids
-          const long long* __restrict__ tab = static_cast<const long long*>(op.p0);
-          store_i64x4(static_cast<long long*>(out), 4 * q, __ldg(tab + __float_as_uint(raw[u].x)), __ldg(tab + __float_as_uint(raw[u].y)),
-                      __ldg(tab + __float_as_uint(raw[u].z)), __ldg(tab + __float_as_uint(raw[u].w)));
-          break;
-        }
-        default: {  // TXF_OP_RATIO_LABEL: second fp32 column (tips)
-          const float4 t = fill_f4(ldg_f4(v1 + 4 * q), quad_valid(valid1, 4 * q));
-          store_i64x4(static_cast<long long*>(out), 4 * q, label1(x.x, t.x, p.ratio), label1(x.y, t.y, p.ratio), label1(x.z, t.z, p.ratio),
-                      label1(x.w, t.w, p.ratio));
-          break;
-        }
-      }
-    }
-  }
-  // offsets has n + 1 entries; entry n is written here when n % 4 == 0, else by the scalar tail
-  if (kind == TXF_OP_FILL_STR && blockIdx.x == 0 && threadIdx.x == 0) {
-    const int32_t* off = static_cast<const int32_t*>(op.in0);
-    static_cast<int32_t*>(out)[4 * nquads] = off[4 * nquads] - p.base;
-  }
-}
-
-// ops whose input cells are 8 bytes: int64 z-score / bucketize / fill
-__device__ __forceinline__ void run_in8(const XfOp& op, const uint8_t* smem, int64_t nquads) {
-  const NumParams p = make_params(op, smem);
-  const int kind = op.kind;
-  const long long* __restrict__ v = static_cast<const long long*>(op.in0);
-  const uint8_t* __restrict__ valid = op.valid0;
-  void* out = op.out;
-  TXF_FOR_EACH_TILE(nquads) {
-#pragma unroll 1
-    for (int h = 0; h < 2; ++h) {
-      longlong2 ra[2], rb[2];
-      uint32_t m[2];
-#pragma unroll
-      for (int u = 0; u < 2; ++u) {
-        int64_t q = q0 + static_cast<int64_t>(2 * h + u) * kXfBlock;
-        ra[u] = make_longlong2(0, 0); rb[u] = make_longlong2(0, 0); m[u] = 0;
-        if (q < nquads) { ra[u] = ldg_l2(v + 4 * q); rb[u] = ldg_l2(v + 4 * q + 2); m[u] = quad_valid(valid, 4 * q); }
-      }
-#pragma unroll
-      for (int u = 0; u < 2; ++u) {
-        int64_t q = q0 + static_cast<int64_t>(2 * h + u) * kXfBlock;
-        if (q >= nquads) continue;
-        const long long a = m[u] & 1 ? ra[u].x : 0LL, b = m[u] & 2 ? ra[u].y : 0LL, c = m[u] & 4 ? rb[u].x : 0LL,
-                        d = m[u] & 8 ? rb[u].y : 0LL;
-        switch (kind) {
-          case TXF_OP_FILL_I64:
-            store_i64x4(static_cast<long long*>(out), 4 * q, a, b, c, d);
-            break;
-          case TXF_OP_ZSCORE:
-            stcs_f4(static_cast<float*>(out) + 4 * q, make_float4(zscore1(i64_to_f32(a), p.z), zscore1(i64_to_f32(b), p.z),
-                                                                  zscore1(i64_to_f32(c), p.z), zscore1(i64_to_f32(d), p.z)));
-            break;
-          default:  // TXF_OP_BUCKETIZE
-          {
-            long long id[4];
-            bucket_quad(make_float4(i64_to_f32(a), i64_to_f32(b), i64_to_f32(c), i64_to_f32(d)), p, id);
-            store_i64x4(static_cast<long long*>(out), 4 * q, id[0], id[1], id[2], id[3]);
-          }
-            break;
-        }
-      }
-    }
-  }
-}
-
 // Vocabulary op: row tiles of kXfVocabTileRows rows; the tile's term bytes are staged in shared
 // memory (coalesced 16-byte loads), then one row per lane: coalesced offsets in, coalesced ids out.
 __device__ __forceinline__ void run_vocab(const XfOp& op, const uint8_t* smem, uint8_t* stage, int64_t n) {
@@ -368,9 +233,10 @@ __device__ __forceinline__ void run_vocab(const XfOp& op, const uint8_t* smem, u
   __syncthreads();  // the pipe's shared memory is re-initialised by the next vocabulary op
 }
 
-__global__ void __launch_bounds__(kXfBlock, 1) transform_kernel(const __grid_constant__ XfProgram prog, int64_t n) {
+// String-lookup ops (TXF_OP_VOCAB: a table that was not analyzed, e.g. TransformDataset on new data
+// or a loaded state): one persistent CTA per SM; lookup tables are staged in shared memory once.
+__global__ void __launch_bounds__(kXfBlock, 1) transform_strings_kernel(const __grid_constant__ XfProgram prog, int64_t n) {
   extern __shared__ __align__(16) uint8_t smem[];
-  // the op table is copied to shared memory so the tile functions can take plain pointers to it
   __shared__ XfOp s_ops[TXF_MAX_OPS];
   const int nops = prog.nops;
   {
@@ -379,37 +245,15 @@ __global__ void __launch_bounds__(kXfBlock, 1) transform_kernel(const __grid_con
     for (int i = threadIdx.x; i < nops * static_cast<int>(sizeof(XfOp) / 4); i += kXfBlock) dst[i] = src[i];
   }
   __syncthreads();
-  // ---- stage read-mostly state once per CTA ----------------------------------------------
   for (int o = 0; o < nops; ++o) {
     const XfOp& op = s_ops[o];
     if (op.smem_off < 0) continue;
-    if (op.kind == TXF_OP_BUCKETIZE) {
-      int nb = *static_cast<const int32_t*>(op.p1);
-      float* dst = reinterpret_cast<float*>(smem + op.smem_off);
-      for (int i = threadIdx.x; i < nb; i += kXfBlock) dst[i] = static_cast<const float*>(op.p0)[i];
-    } else if (op.kind == TXF_OP_VOCAB) {
-      unsigned long long* dst = reinterpret_cast<unsigned long long*>(smem + op.smem_off);
-      const unsigned long long* src = static_cast<const unsigned long long*>(op.p0);
-      for (int64_t i = threadIdx.x; i < op.a0 * 3; i += kXfBlock) dst[i] = src[i];
-    }
+    unsigned long long* dst = reinterpret_cast<unsigned long long*>(smem + op.smem_off);
+    const unsigned long long* src = static_cast<const unsigned long long*>(op.p0);
+    for (int64_t i = threadIdx.x; i < op.a0 * 3; i += kXfBlock) dst[i] = src[i];
   }
   __syncthreads();
-
-  const int64_t nquads = n >> 2;
-  for (int o = 0; o < nops; ++o) {
-    const XfOp& op = s_ops[o];
-    if (op.kind == TXF_OP_VOCAB)
-      run_vocab(op, smem, smem + prog.stage_off, n);
-    else if (op.kind == TXF_OP_FILL_I64 || ((op.kind == TXF_OP_ZSCORE || op.kind == TXF_OP_BUCKETIZE) && op.in_dtype == TXF_I64))
-      run_in8(op, smem, nquads);
-    else
-      run_in4(op, smem, nquads);
-  }
-  // ---- rows past the last full quad (at most 3) -------------------------------------------
-  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
-    int64_t row = (nquads << 2) + threadIdx.x;
-    for (int o = 0; o < nops; ++o) op_row(s_ops[o], smem, row, n);
-  }
+  for (int o = 0; o < nops; ++o) run_vocab(s_ops[o], smem, smem + prog.stage_off, n);
 }
 
 // ---- numeric ops as one grid of (op, tile) blocks ----------------------------------------------
@@ -641,10 +485,10 @@ int txf_transform(const txf_op* ops, int nops, int64_t n, txf_stream_t stream) {
     vprog.smem_bytes = smem;
     vprog.stage_off = 0;
     if (smem > 48 * 1024)
-      TXF_CUDA(cudaFuncSetAttribute(transform_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    int64_t ntiles = (n + kXfTileRows - 1) / kXfTileRows;
+      TXF_CUDA(cudaFuncSetAttribute(transform_strings_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    int64_t ntiles = (n + kXfVocabTileRows - 1) / kXfVocabTileRows;
     int grid = static_cast<int>(ntiles < kSMs ? ntiles : kSMs);
-    transform_kernel<<<grid, kXfBlock, smem, cs>>>(vprog, n);
+    transform_strings_kernel<<<grid, kXfBlock, smem, cs>>>(vprog, n);
     TXF_LAUNCH_CHECK();
     count_launch(1);
     if (!tp.prog.nops) { g_last_grid = grid; g_last_block = kXfBlock; g_last_smem = smem; }
