@@ -18,7 +18,7 @@ def main():
         if r[im] == "gpu__time_duration.sum":
             launches[int(r[iid])] = (r[ik].split("(")[0].replace("void ", "").strip(), float(r[iv].replace(",", "")) / 1e3)
     names = list(launches.values())
-    tidx = [i for i, (k, _) in enumerate(names) if k.startswith("transform_kernel")]
+    tidx = [i for i, (k, _) in enumerate(names) if k.startswith("transform_")]
     print("launches", len(names))
     print("transform idx", tidx)
     lo = tidx[-2] + 1 if len(tidx) > 1 else 0
