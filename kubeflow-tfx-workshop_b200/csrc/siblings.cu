@@ -220,6 +220,13 @@ __global__ void i64_format_write_kernel(const long long* __restrict__ v, const u
   } while (m);
 }
 
+// one-shot grid for the streaming maps: one quad per thread (tools/probes/copy_probe.cu: one-shot
+// 256-thread blocks move more bytes per second here than a capped, grid-striding launch)
+static unsigned map_grid(int64_t n) {
+  const int64_t need = ((n >> 2) + kSibBlock - 1) / kSibBlock;
+  return static_cast<unsigned>(need < 1 ? 1 : need);
+}
+
 static int sib_grid(int64_t n) {
   const int64_t need = ((n >> 2) + kSibBlock - 1) / kSibBlock;
   return static_cast<int>(need < 1 ? 1 : (need < kSibGrid ? need : kSibGrid));
@@ -302,7 +309,7 @@ int txf_map_binary(int opcode, const txf_operand* a, const txf_operand* b, float
   TXF_REQUIRE(out_dev != nullptr && aligned(out_dev, 16), "map_binary: output null or not 16B aligned");
   TXF_REQUIRE(n >= 0 && n < (1LL << 31), "map_binary: n out of range");
   if (n == 0) return TXF_OK;
-  const int grid = sib_grid(n);
+  const unsigned grid = map_grid(n);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   switch (opcode) {
     case TXF_ARITH_ADD: map_binary_kernel<TXF_ARITH_ADD><<<grid, kSibBlock, 0, s>>>(da, db, out_dev, n); break;
@@ -326,7 +333,7 @@ int txf_map_cast(const txf_operand* x, int to_dtype, void* out_dev, int64_t n, t
   TXF_REQUIRE(out_dev != nullptr && aligned(out_dev, 16), "map_cast: output null or not 16B aligned");
   TXF_REQUIRE(n >= 0 && n < (1LL << 31), "map_cast: n out of range");
   if (n == 0) return TXF_OK;
-  map_cast_kernel<<<sib_grid(n), kSibBlock, 0, static_cast<cudaStream_t>(stream)>>>(dx, to_dtype, out_dev, n);
+  map_cast_kernel<<<map_grid(n), kSibBlock, 0, static_cast<cudaStream_t>(stream)>>>(dx, to_dtype, out_dev, n);
   TXF_LAUNCH_CHECK();
   count_launch(1);
   return TXF_OK;
@@ -370,7 +377,7 @@ int txf_map_scale_minmax(const txf_operand* x, const float* minmax_dev, float ou
   TXF_REQUIRE(out_dev != nullptr && aligned(out_dev, 16), "map_scale_minmax: output null or not 16B aligned");
   TXF_REQUIRE(n >= 0 && n < (1LL << 31), "map_scale_minmax: n out of range");
   if (n == 0) return TXF_OK;
-  map_scale_kernel<<<sib_grid(n), kSibBlock, 0, static_cast<cudaStream_t>(stream)>>>(dx, minmax_dev, out_min, out_max, out_dev, n);
+  map_scale_kernel<<<map_grid(n), kSibBlock, 0, static_cast<cudaStream_t>(stream)>>>(dx, minmax_dev, out_min, out_max, out_dev, n);
   TXF_LAUNCH_CHECK();
   count_launch(1);
   return TXF_OK;

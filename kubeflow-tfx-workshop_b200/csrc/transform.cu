@@ -303,19 +303,37 @@ __global__ void __launch_bounds__(kTileThreads) transform_tiles_kernel(const __g
   if (!op_in8(op)) {
     const float* __restrict__ v = static_cast<const float*>(op.in0);
     const uint8_t* __restrict__ valid = (kind == TXF_OP_FILL_STR || kind == TXF_OP_VOCAB_CODED) ? nullptr : op.valid0;
-    const int64_t q0 = tile * kTileQuads4 + threadIdx.x;
+    // Without a validity bitmap a thread's four quads are 256 quads apart (unit-stride warps, the
+    // fastest shape).  With a bitmap a thread owns two PAIRS of adjacent quads instead: the 8 rows of
+    // a pair share exactly one validity byte, so a warp reads its validity as 32 consecutive bytes,
+    // one load per pair -- a byte load per quad cost 25-30 % on every 4-byte op, the 32-byte stride
+    // of the pairs costs 8 %.
+    const bool paired = valid != nullptr;  // block-uniform
+    const int64_t q0 = tile * kTileQuads4 + threadIdx.x, p0 = tile * (kTileQuads4 / 2) + threadIdx.x;
+    auto quad_of = [&](int u) -> int64_t { return paired ? 2 * (p0 + (u >> 1) * kTileThreads) + (u & 1) : q0 + u * kTileThreads; };
     float4 raw[4];
     uint32_t m[4];
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
-      const int64_t q = q0 + u * kTileThreads;
+      const int64_t q = quad_of(u);
       raw[u] = make_float4(0.f, 0.f, 0.f, 0.f);
       m[u] = 0;
-      if (q < nquads) { raw[u] = ldg_f4(v + 4 * q); m[u] = quad_valid(valid, 4 * q); }
+      if (q < nquads) { raw[u] = ldg_f4(v + 4 * q); m[u] = 0xFu; }
+    }
+    if (paired) {
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const int64_t q = quad_of(2 * j);
+        if (q < nquads) {
+          const uint32_t vb = __ldg(valid + (q >> 1));
+          m[2 * j] = vb & 0xFu;
+          m[2 * j + 1] &= vb >> 4;
+        }
+      }
     }
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
-      const int64_t q = q0 + u * kTileThreads;
+      const int64_t q = quad_of(u);
       if (q >= nquads) continue;
       const float4 x = fill_f4(raw[u], m[u]);
       switch (kind) {
