@@ -242,7 +242,7 @@ TXF_API int txf_transform_launch_info(int* grid, int* block, int* smem_bytes);
  * CsvExampleGen (airflow-dags/taxi_pipeline.py:70-73) and the typed CSV -> Example loop of
  * notebooks/04_TensorFlow_Model_Analysis.ipynb:222-240: the text of the file, copied to the device
  * once, becomes int64 / float32 / string columns with validity bitmaps.  Records are lines; fields
- * may be quoted ("" = escaped quote); an empty unquoted field is a missing value.
+ * may be quoted ("" = escaped quote); an empty field, quoted or not, is a missing value.
  *   text_dev: 16-byte aligned, with at least 16 readable bytes past nbytes; nbytes < 2^31.
  *   1. txf_csv_count_lines -> block_lines_dev[ceil(nbytes / txf_csv_block_bytes())] ('\n' per block)
  *   2. caller: exclusive prefix sum -> block_base_dev (int64); nlines = sum (+1 if the text does

@@ -296,7 +296,7 @@ __global__ void __launch_bounds__(kCsvThreads) csv_scan_rows_kernel(const uint8_
       }
     }
     const uint32_t n = static_cast<uint32_t>(f1 - f0);
-    const bool has = present_field && (n > 0 || quoted);  // a quoted empty string is a value; an empty field is missing
+    const bool has = present_field && n > 0;  // an empty field is a missing value, quoted or not (the reference tests value == '')
     auto get = [&](uint32_t k) -> uint32_t { return at(f0 + k); };
     if (MODE == 0) {
       uint32_t fl = 0;

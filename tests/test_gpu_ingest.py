@@ -150,3 +150,40 @@ def test_ingested_table_feeds_the_transform(ktw):
             assert a[k] == c.to_list(), k
         else:
             assert torch.equal(a[k], c.values), k
+
+
+def test_fuzz_small_files_against_csv_module(ktw):
+    """300 small random files written by Python's csv.writer (quoting of commas / quotes / spaces,
+    empty and quoted-empty fields, one to twelve columns, with and without a final newline, CRLF)
+    parsed with a given schema: every cell must equal the csv module + int()/float()/bytes."""
+    rng = np.random.default_rng(2024)
+    texts = ["", "a", "a,b", 'say "x"', "  lead", "trail  ", "ünï", "7", "-3.5e2", ",", '"', "x" * 40]
+
+    def cell(kind):
+        if rng.random() < 0.2:
+            return ""
+        if kind == "int64":
+            return str(int(rng.integers(-10 ** int(rng.integers(1, 19)), 10 ** int(rng.integers(1, 19)))))
+        if kind == "float32":
+            v = float(rng.standard_normal() * 10.0 ** int(rng.integers(-12, 12)))
+            return [repr(v), "%.3f" % v, "%e" % v, str(int(v)) if abs(v) < 1e15 else repr(v), "%.10g" % v][int(rng.integers(0, 5))]
+        return texts[int(rng.integers(0, len(texts)))]
+
+    for trial in range(300):
+        ncols, nrows = int(rng.integers(1, 13)), int(rng.integers(0, 41))
+        kinds = {f"c{j}": ["int64", "float32", "bytes"][int(rng.integers(0, 3))] for j in range(ncols)}
+        buf = io.StringIO()
+        w = csv.writer(buf, lineterminator="\r\n" if trial % 3 == 0 else "\n")
+        w.writerow(list(kinds))
+        for _ in range(nrows):
+            row = [cell(k) for k in kinds.values()]
+            if ncols == 1 and row[0] == "":
+                row[0] = "1" if kinds["c0"] != "bytes" else "z"  # a lone empty field is a blank line
+            w.writerow(row)
+        text = buf.getvalue()
+        if trial % 2:
+            text = text.rstrip("\r\n")
+        data = text.encode("utf-8")
+        table = ktw.read_csv(data, schema=kinds)
+        assert len(table) == nrows, (trial, text)
+        check_table(table, python_parse(data, kinds))
