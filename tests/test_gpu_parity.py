@@ -136,6 +136,24 @@ def test_synthetic_taxi(ktw, fn, n, force_general):
     check_outputs(out, want, wstate)
 
 
+def test_ragged_sizes_around_kernel_tile_edges(ktw, fn):
+    """Row counts around every tiling unit of the kernels (quads of 4, warps of 32, 96-row steps of
+    the vocabulary count, 1024-quad transform tiles, 3072 = 32 warps x 96 rows): state and every
+    output against the oracle, through both the coded and the string vocabulary path."""
+    from kubeflow_tfx_workshop_b200 import synth
+    eng = ktw.Engine(ktw.trace(fn, synth.TAXI_SCHEMA))
+    for n in (2, 3, 4, 5, 31, 32, 33, 95, 96, 97, 191, 192, 193, 1023, 1024, 1025, 3071, 3072, 3073, 4095, 4096, 4097, 8193, 12289):
+        host = synth.taxi_table(n, seed=n, backend="numpy")
+        dev = host.to("cuda")
+        out, state = eng.analyze_and_transform(dev)
+        want, wstate = O.analyze_and_transform(helpers.oracle_from_table(host))
+        check_state(state, wstate)
+        check_outputs(out, want, wstate)
+        eng.use_codes = False
+        check_outputs(eng.transform(dev, state), want, wstate)
+        eng.use_codes = True
+
+
 def test_coded_and_string_vocabulary_paths_agree(ktw, fn):
     """Transform of the analyzed table decodes dictionary codes; any other table re-reads the term
     bytes.  Both must give the oracle's ids."""
