@@ -116,7 +116,7 @@ __device__ __noinline__ int vc_find_slow(unsigned long long* s_a, unsigned long 
 
 // Count one term per lane (has == false: the lane only takes part in the warp votes).  Must be
 // called by all 32 lanes of a warp together.
-__device__ __forceinline__ int vc_count(const VcFront& f, bool has, StrKey key, int64_t row, int32_t b, uint32_t len) {
+__device__ __forceinline__ int vc_count(const VcFront& f, bool has, StrKey key, uint32_t row, int32_t b, uint32_t len) {
   int slot = -1;
   if (has) {
     const uint32_t idx = static_cast<uint32_t>(home_slot(key.a, key.b, kVcSlots - 1));
@@ -124,7 +124,7 @@ __device__ __forceinline__ int vc_count(const VcFront& f, bool has, StrKey key, 
     const unsigned long long a0 = *reinterpret_cast<volatile unsigned long long*>(&f.s_a[idx]);
     const unsigned long long b0 = *reinterpret_cast<volatile unsigned long long*>(&f.s_b[idx]);
     slot = (a0 == key.a && b0 == key.b) ? static_cast<int>(idx)
-                                        : vc_find_slow(f.s_a, f.s_b, f.s_row, key.a, key.b, idx, static_cast<uint32_t>(row));
+                                        : vc_find_slow(f.s_a, f.s_b, f.s_row, key.a, key.b, idx, row);
   }
   // one warp-level aggregation round (absorbs the dominant term), then one atomic per lane
   const unsigned hits = __ballot_sync(0xffffffffu, slot >= 0);
@@ -191,7 +191,7 @@ __device__ __forceinline__ void vc_issue(const VcSource& src, const VcStage& st,
 // instructions) and queues the long ones; phase B hashes the queued terms with the lanes packed --
 // columns that mix empty/short and long terms would otherwise idle most lanes during the hashing.
 template <bool STAGED, bool META>
-__device__ __forceinline__ void vc_step(const VcFront& f, const VcSource& src, const VcStage& st, int64_t r0, int64_t r1,
+__device__ __forceinline__ void vc_step(const VcFront& f, const VcSource& src, const VcStage& st, uint32_t r0, uint32_t r1,
                                         uint16_t* wqueue, const uint4* s_mask, int& empty_slot) {
   const int32_t* soff = st.off();
   const uint8_t* base = STAGED ? st.bytes() - st.a0() : src.pool;       // the term at pool offset o is at base + o
@@ -199,7 +199,7 @@ __device__ __forceinline__ void vc_step(const VcFront& f, const VcSource& src, c
   uint32_t nq = 0;
 #pragma unroll
   for (int j = 0; j < kVcRowsPerLane; ++j) {
-    const int64_t row = r0 + j * 32 + lane_id();
+    const uint32_t row = r0 + j * 32 + lane_id();  // rows fit 31 bits (the entry point checks n)
     const bool in_step = row < r1;
     int32_t b = 0;
     uint32_t len = 0;
@@ -234,7 +234,7 @@ __device__ __forceinline__ void vc_step(const VcFront& f, const VcSource& src, c
   for (uint32_t t0 = 0; t0 < nq; t0 += 32) {  // warp-uniform trip count
     const uint32_t t = t0 + lane_id();
     const bool has = t < nq;
-    int64_t row = r0;
+    uint32_t row = r0;
     int32_t b = 0;
     uint32_t len = 0;
     StrKey key{0, 0};
@@ -293,9 +293,9 @@ __global__ void __launch_bounds__(kVcBlock, 1) vocab_count_kernel(const int32_t*
     const int64_t r0 = t * kVcStepRows, r1 = step_end(t);
     mbar_wait(&bars[s], (k >> 1) & 1u);
     const VcStage st{wbase + s * kVcStageBytes};
-    if (st.staged() && st.meta()) vc_step<true, true>(f, src, st, r0, r1, wqueue, s_mask, empty_slot);
-    else if (st.staged()) vc_step<true, false>(f, src, st, r0, r1, wqueue, s_mask, empty_slot);
-    else vc_step<false, false>(f, src, st, r0, r1, wqueue, s_mask, empty_slot);
+    if (st.staged() && st.meta()) vc_step<true, true>(f, src, st, static_cast<uint32_t>(r0), static_cast<uint32_t>(r1), wqueue, s_mask, empty_slot);
+    else if (st.staged()) vc_step<true, false>(f, src, st, static_cast<uint32_t>(r0), static_cast<uint32_t>(r1), wqueue, s_mask, empty_slot);
+    else vc_step<false, false>(f, src, st, static_cast<uint32_t>(r0), static_cast<uint32_t>(r1), wqueue, s_mask, empty_slot);
     __syncwarp();  // every lane is done with the stage: refill it with the step after next
     const int64_t nxt = t + 2 * nw;
     if (lane_id() == 0 && nxt < nsteps) vc_issue(src, st, &bars[s], nxt * kVcStepRows, step_end(nxt));
