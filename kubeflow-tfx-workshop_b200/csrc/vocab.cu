@@ -167,12 +167,12 @@ struct VcSource {
 };
 
 // lane 0 of the owning warp: start the copies of step rows [r0, r1) into the stage
-__device__ __forceinline__ void vc_issue(const VcSource& src, const VcStage& st, uint64_t* bar, int64_t r0, int64_t r1) {
+__device__ __forceinline__ void vc_issue(const VcSource& src, const VcStage& st, uint64_t* bar, uint32_t r0, uint32_t r1) {
   const long long b0 = __ldg(src.offsets + r0), e0 = __ldg(src.offsets + r1);
   const long long start = b0 & ~15LL;
   const long long need = ((e0 - start + 15) & ~15LL) + 32;  // window loads touch < 24 bytes past a term
   const bool do_bytes = src.pool_ok && need <= kVcStageCap;
-  const bool do_meta = src.off_ok && (r1 - r0) == kVcStepRows && r0 + kVcOffSlots <= src.n + 1;
+  const bool do_meta = src.off_ok && (r1 - r0) == kVcStepRows && static_cast<int64_t>(r0) + kVcOffSlots <= src.n + 1;
   st.a0() = start;
   st.staged() = do_bytes;
   st.meta() = do_meta;
@@ -279,25 +279,27 @@ __global__ void __launch_bounds__(kVcBlock, 1) vocab_count_kernel(const int32_t*
   }
   __syncthreads();  // table zeroed, barriers initialised: the only block-wide barrier before the flush
 
-  const int64_t nsteps = (n + kVcStepRows - 1) / kVcStepRows;
-  const int64_t gw = static_cast<int64_t>(blockIdx.x) * kVcWarps + warp, nw = static_cast<int64_t>(gridDim.x) * kVcWarps;
-  auto step_end = [&](int64_t t) { return (t + 1) * kVcStepRows < n ? (t + 1) * kVcStepRows : n; };
+  // rows fit 31 bits (the entry point checks n), so steps and rows are 32-bit inside the loop
+  const uint32_t n32 = static_cast<uint32_t>(n);
+  const uint32_t nsteps = (n32 + kVcStepRows - 1) / kVcStepRows;
+  const uint32_t gw = blockIdx.x * kVcWarps + warp, nw = gridDim.x * kVcWarps;
+  auto step_end = [&](uint32_t t) { return (t + 1) * kVcStepRows < n32 ? (t + 1) * kVcStepRows : n32; };
   if (lane_id() == 0) {
     if (gw < nsteps) vc_issue(src, VcStage{wbase}, &bars[0], gw * kVcStepRows, step_end(gw));
     if (gw + nw < nsteps) vc_issue(src, VcStage{wbase + kVcStageBytes}, &bars[1], (gw + nw) * kVcStepRows, step_end(gw + nw));
   }
   uint32_t k = 0;
   int empty_slot = -1;  // front-table slot of the empty term once this warp has met it (warp-uniform)
-  for (int64_t t = gw; t < nsteps; t += nw, ++k) {
+  for (uint32_t t = gw; t < nsteps; t += nw, ++k) {
     const int s = k & 1;
-    const int64_t r0 = t * kVcStepRows, r1 = step_end(t);
+    const uint32_t r0 = t * kVcStepRows, r1 = step_end(t);
     mbar_wait(&bars[s], (k >> 1) & 1u);
     const VcStage st{wbase + s * kVcStageBytes};
-    if (st.staged() && st.meta()) vc_step<true, true>(f, src, st, static_cast<uint32_t>(r0), static_cast<uint32_t>(r1), wqueue, s_mask, empty_slot);
-    else if (st.staged()) vc_step<true, false>(f, src, st, static_cast<uint32_t>(r0), static_cast<uint32_t>(r1), wqueue, s_mask, empty_slot);
-    else vc_step<false, false>(f, src, st, static_cast<uint32_t>(r0), static_cast<uint32_t>(r1), wqueue, s_mask, empty_slot);
+    if (st.staged() && st.meta()) vc_step<true, true>(f, src, st, r0, r1, wqueue, s_mask, empty_slot);
+    else if (st.staged()) vc_step<true, false>(f, src, st, r0, r1, wqueue, s_mask, empty_slot);
+    else vc_step<false, false>(f, src, st, r0, r1, wqueue, s_mask, empty_slot);
     __syncwarp();  // every lane is done with the stage: refill it with the step after next
-    const int64_t nxt = t + 2 * nw;
+    const uint32_t nxt = t + 2 * nw;
     if (lane_id() == 0 && nxt < nsteps) vc_issue(src, st, &bars[s], nxt * kVcStepRows, step_end(nxt));
   }
   __syncthreads();
