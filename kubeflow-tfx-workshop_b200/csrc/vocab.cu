@@ -148,10 +148,10 @@ __device__ __forceinline__ int vc_count(const VcFront& f, bool has, StrKey key, 
 // completion on the stage's mbarrier), the warp waits on that barrier only, counts, and re-arms the
 // stage for the step after next.  No block-wide barrier exists between the table initialisation and
 // the final flush, so no warp ever waits for another one.
-// Stage layout: [a0: pool offset of byte 0 (8) | staged (4) | meta (4)] [offsets x 100] [bytes].
+// Stage layout: [a0: pool offset of byte 0 (4) | pad (4) | staged (4) | meta (4)] [offsets x 100] [bytes].
 struct VcStage {
   uint8_t* base;  // generic pointer to the stage
-  __device__ __forceinline__ long long& a0() const { return *reinterpret_cast<long long*>(base); }
+  __device__ __forceinline__ uint32_t& a0() const { return *reinterpret_cast<uint32_t*>(base); }  // pools hold < 2^31 bytes
   __device__ __forceinline__ int& staged() const { return *reinterpret_cast<int*>(base + 8); }
   __device__ __forceinline__ int& meta() const { return *reinterpret_cast<int*>(base + 12); }
   __device__ __forceinline__ int32_t* off() const { return reinterpret_cast<int32_t*>(base + 16); }
@@ -168,22 +168,22 @@ struct VcSource {
 
 // lane 0 of the owning warp: start the copies of step rows [r0, r1) into the stage
 __device__ __forceinline__ void vc_issue(const VcSource& src, const VcStage& st, uint64_t* bar, uint32_t r0, uint32_t r1) {
-  const long long b0 = __ldg(src.offsets + r0), e0 = __ldg(src.offsets + r1);
-  const long long start = b0 & ~15LL;
-  const long long need = ((e0 - start + 15) & ~15LL) + 32;  // window loads touch < 24 bytes past a term
-  const bool do_bytes = src.pool_ok && need <= kVcStageCap;
+  const uint32_t b0 = static_cast<uint32_t>(__ldg(src.offsets + r0)), e0 = static_cast<uint32_t>(__ldg(src.offsets + r1));
+  const uint32_t start = b0 & ~15u;
+  const uint32_t need = ((e0 - start + 15u) & ~15u) + 32u;  // window loads touch < 24 bytes past a term
+  const bool do_bytes = src.pool_ok && need <= static_cast<uint32_t>(kVcStageCap);
   const bool do_meta = src.off_ok && (r1 - r0) == kVcStepRows && static_cast<int64_t>(r0) + kVcOffSlots <= src.n + 1;
   st.a0() = start;
   st.staged() = do_bytes;
   st.meta() = do_meta;
-  const uint32_t total = (do_bytes ? static_cast<uint32_t>(need) : 0u) + (do_meta ? kVcOffSlots * 4u : 0u);
+  const uint32_t total = (do_bytes ? need : 0u) + (do_meta ? kVcOffSlots * 4u : 0u);
   if (total == 0) {
     mbar_arrive(bar);
     return;
   }
   fence_proxy_async();  // the stage was read through ordinary loads until now
   mbar_arrive_expect_tx(bar, total);
-  if (do_bytes) bulk_copy_g2s(st.bytes(), src.pool + start, static_cast<uint32_t>(need), bar);
+  if (do_bytes) bulk_copy_g2s(st.bytes(), src.pool + start, need, bar);
   if (do_meta) bulk_copy_g2s(st.off(), src.offsets + r0, kVcOffSlots * 4u, bar);
 }
 
@@ -195,7 +195,7 @@ __device__ __forceinline__ void vc_step(const VcFront& f, const VcSource& src, c
                                         uint16_t* wqueue, const uint4* s_mask, int& empty_slot) {
   const int32_t* soff = st.off();
   const uint8_t* base = STAGED ? st.bytes() - st.a0() : src.pool;       // the term at pool offset o is at base + o
-  const uint32_t sbase = STAGED ? smem_u32(st.bytes()) - static_cast<uint32_t>(st.a0()) : 0u;
+  const uint32_t sbase = STAGED ? smem_u32(st.bytes()) - st.a0() : 0u;
   uint32_t nq = 0;
 #pragma unroll
   for (int j = 0; j < kVcRowsPerLane; ++j) {
