@@ -360,7 +360,7 @@ __global__ void __launch_bounds__(kQBlock) qcount_kernel(NumColsView cols, int64
   };
   auto visit = [&](uint32_t key) { count(key, lookup(key)); };
   // the four table lookups of a quad are issued together (independent loads), then the counters
-  auto visit_quad = [&](float4 x, uint32_t vbyte, int64_t q) {  // vbyte: raw bitmap byte of the quad (prefetched)
+  auto visit_quad = [&](float4 x, uint32_t vbyte, uint32_t q) {  // vbyte: raw bitmap byte of the quad (prefetched)
     const uint32_t m = valid == nullptr ? 0xFu : (vbyte >> ((4 * q) & 4)) & 0xFu;
     const uint32_t k0 = f32_key(m & 1 ? x.x : 0.f), k1 = f32_key(m & 2 ? x.y : 0.f), k2 = f32_key(m & 4 ? x.z : 0.f),
                    k3 = f32_key(m & 8 ? x.w : 0.f);
@@ -380,14 +380,15 @@ __global__ void __launch_bounds__(kQBlock) qcount_kernel(NumColsView cols, int64
     __syncthreads();
   };
 
-  const int64_t nquads = n >> 2;
-  const int64_t ntiles = (nquads + kQTileQuads - 1) / kQTileQuads;
-  int64_t tile = blockIdx.x;
+  // n < 2^31 (checked by the entry point): quads and tiles are 32-bit inside the loop
+  const uint32_t nquads = static_cast<uint32_t>(n >> 2);
+  const uint32_t ntiles = (nquads + kQTileQuads - 1) / kQTileQuads;
+  uint32_t tile = blockIdx.x;
   float4 xa = make_float4(0, 0, 0, 0), xb = xa;
   uint32_t va = 0, vb = 0;  // raw validity bytes: decoded at use, so the prefetch never waits on them
   bool ha = false, hb = false;
-  auto load_tile = [&](int64_t t) {
-    const int64_t qa = t * kQTileQuads + threadIdx.x, qb = qa + kQBlock;
+  auto load_tile = [&](uint32_t t) {
+    const uint32_t qa = t * kQTileQuads + threadIdx.x, qb = qa + kQBlock;
     ha = t < ntiles && qa < nquads;
     hb = t < ntiles && qb < nquads;
     if (ha) { xa = load_quad_as_f32<F32>(values, qa); if (valid) va = __ldg(valid + (qa >> 1)); }
@@ -398,7 +399,7 @@ __global__ void __launch_bounds__(kQBlock) qcount_kernel(NumColsView cols, int64
     const float4 ca = xa, cb = xb;
     const uint32_t cva = va, cvb = vb;
     const bool cha = ha, chb = hb;
-    const int64_t qa = tile * kQTileQuads + threadIdx.x;
+    const uint32_t qa = tile * kQTileQuads + threadIdx.x;
     load_tile(tile + gridDim.x);  // prefetch
     if (cha) visit_quad(ca, cva, qa);
     if (chb) visit_quad(cb, cvb, qa + kQBlock);
@@ -406,7 +407,7 @@ __global__ void __launch_bounds__(kQBlock) qcount_kernel(NumColsView cols, int64
     if ((it & 3) == 0 && __syncthreads_or(s_ncand > kQCandBuf / 2)) flush();
   }
   if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {  // rows past the last full quad
-    const int64_t i = (nquads << 2) + threadIdx.x;
+    const int64_t i = (static_cast<int64_t>(nquads) << 2) + threadIdx.x;
     const bool present = row_valid(valid, i);
     visit(F32 ? cell_key_f32(static_cast<const float*>(values)[i], present)
               : cell_key_i64(static_cast<const long long*>(values)[i], present));
