@@ -64,10 +64,18 @@ __host__ __device__ __forceinline__ float bits_f32(uint32_t u) {
 #endif
 }
 __host__ __device__ __forceinline__ uint32_t f32_key(float x) {
+#ifdef __CUDA_ARCH__
+  // same function in seven instructions: x + 0 turns -0 into +0, the sign is spread by an
+  // arithmetic shift (negative: flip all bits, else set the top bit), NaNs are overridden last
+  const uint32_t u = __float_as_uint(__fadd_rn(x, 0.0f));
+  const uint32_t k = u ^ (static_cast<uint32_t>(static_cast<int32_t>(u) >> 31) | 0x80000000u);
+  return (u & 0x7FFFFFFFu) > 0x7F800000u ? 0xFFFFFFFFu : k;
+#else
   uint32_t u = f32_bits(x);
   if ((u & 0x7FFFFFFFu) > 0x7F800000u) return 0xFFFFFFFFu;  // any NaN
   if (u == 0x80000000u) u = 0u;                               // -0 -> +0
   return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+#endif
 }
 __host__ __device__ __forceinline__ float key_f32(uint32_t k) {
   return bits_f32((k & 0x80000000u) ? (k & 0x7FFFFFFFu) : ~k);
