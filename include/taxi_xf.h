@@ -137,10 +137,17 @@ TXF_API int txf_qfinal(const uint32_t* direct_key_dev, const uint64_t* cand_rank
  * term identity, first-seen bytes kept in an arena, then the top_k terms by (count, bytes)
  * descending.  Fingerprint64 is evaluated only for out-of-vocabulary terms.
  *
- * table: capacity (power of two) slots of 32 bytes {u64 a, u64 b, u64 count, u64 strref}, (a, b) being
- * the term's 128-bit identity (the bytes themselves up to 15 bytes, a double hash beyond);
- * ctrl_dev: u64[8] = {arena_used, slots_used, overflow, kept, total, sel, 0, 0}.
- * Both must be zero-initialised by the caller before the first count.
+ * table: capacity (power of two) slots of 32 bytes {u64 a, u64 b, u64 count, u64 strref}.  (a, b) is
+ * the term's key: the bytes themselves up to 15 bytes; beyond that a fingerprint (119 hash bits + the
+ * exact length) that only pre-filters -- in this table, in the id lookup and in the decode table every
+ * match of a longer term is confirmed on its bytes (tft counts byte strings), so a fingerprint
+ * collision there never merges two terms.  (The count pass keeps a per-CTA cache in shared memory in
+ * front of this table; the cache alone trusts the full fingerprint.);
+ * ctrl_dev: u64[8] = {arena_used, slots_used, flags, kept, total, sel, dropped, 0}; flags: 1 = arena
+ * full, 2 = table full, 4 = a fixed-layout exchange section overflowed, 16 = a count exceeds 2^32-1
+ * (the top-k cut-off is selected on 32-bit counts), 32 = internal wait limit, 64 = some rank's local
+ * pass overflowed (its flags in bits 8..13).  Table and ctrl must be zero-initialised by the caller
+ * before the first count.  arena_dev must be readable for TXF_POOL_SLACK bytes past arena_cap.
  * ------------------------------------------------------------------------------------------ */
 TXF_API size_t txf_vocab_table_bytes(int64_t capacity);
 /* codes_dev (optional, uint32[n]) receives the dictionary code of every row's term and
@@ -152,11 +159,12 @@ TXF_API int txf_vocab_count(const int32_t* offsets_dev, const uint8_t* pool_dev,
                     void* table_dev, int64_t capacity, uint8_t* arena_dev, int64_t arena_cap,
                     uint64_t* ctrl_dev, uint32_t* codes_dev, uint32_t* local2global_dev, txf_stream_t stream);
 /* final_code_dev: int64[txf_vocab_local_codes() + capacity]; lookup_dev: the vocabulary's lookup
- * table (txf_vocab_build_lookup); semantics of the value = TXF_OP_VOCAB's output for that term */
+ * table (txf_vocab_build_lookup / _lookup_from_terms) and lookup_pool_dev the bytes it was built
+ * over; semantics of the value = TXF_OP_VOCAB's output for that term */
 TXF_API int txf_vocab_final_codes(const void* table_dev, int64_t capacity, const uint8_t* arena_dev,
                           const uint32_t* local2global_dev, const void* lookup_dev, int64_t lookup_cap,
-                          int64_t vocab_size, int64_t num_oov_buckets, int64_t default_value,
-                          int64_t* final_code_dev, txf_stream_t stream);
+                          const uint8_t* lookup_pool_dev, int64_t vocab_size, int64_t num_oov_buckets,
+                          int64_t default_value, int64_t* final_code_dev, txf_stream_t stream);
 /* dense list of occupied slots: ent_dev[capacity] (u32 slot ids), ctrl[4] = total distinct.
  * Terms tft never admits ('' and anything containing \n or \r) are listed last and not
  * counted in ctrl[3] = kept; counts_dev[i] = count of ent_dev[i] saturated to u32. */
@@ -191,8 +199,11 @@ TXF_API int txf_vocab_filter_ge(const uint32_t* ent_dev, const uint32_t* counts_
 TXF_API size_t txf_vocab_sort_scratch_bytes(int64_t m);
 TXF_API int txf_vocab_sort(const void* table_dev, const uint8_t* arena_dev, uint32_t* ent_dev, int64_t m,
                    void* scratch_dev, txf_stream_t stream);
-/* first k sorted entries -> id lookup table (lookup_cap slots of 16 bytes, power of two,
- * >= 2k); the vocabulary's bytes in id order come from txf_vocab_export_* on the same list */
+/* first k sorted entries -> id lookup table of txf_vocab_lookup_bytes(lookup_cap) bytes (lookup_cap:
+ * power of two, >= 2k; 32-byte slots {a, b, strref, id}).  strref points into the byte pool the
+ * table was built over -- arena_dev of the count table here, voc_pool_dev for _lookup_from_terms --
+ * and that pool must stay alive and be passed wherever the table is used (TXF_OP_VOCAB p1,
+ * txf_vocab_final_codes).  The vocabulary's bytes in id order come from txf_vocab_export_* on the same list */
 TXF_API size_t txf_vocab_lookup_bytes(int64_t lookup_cap);
 TXF_API int txf_vocab_build_lookup(const void* table_dev, const uint32_t* ent_sorted_dev, int64_t k, void* lookup_dev,
                            int64_t lookup_cap, txf_stream_t stream);
@@ -206,8 +217,9 @@ TXF_API int txf_vocab_lookup_from_terms(const int32_t* voc_offsets_dev, const ui
  * ------------------------------------------------------------------------------------------ */
 enum {
   TXF_OP_ZSCORE = 0,     /* :116-119  out f32 = (f32(fill(x)) - mean) / sqrt(var); p0 = float[2] {mean,var} */
-  TXF_OP_VOCAB = 1,      /* :121-126  in0 = int32 offsets, pool; p0 = lookup table, a0 = lookup_cap,
-                                       a1 = vocab size, a2 = num_oov_buckets, a3 = default_value; out i64 */
+  TXF_OP_VOCAB = 1,      /* :121-126  in0 = int32 offsets, pool; p0 = lookup table, p1 = the byte pool the
+                                       lookup table was built over, a0 = lookup_cap, a1 = vocab size,
+                                       a2 = num_oov_buckets, a3 = default_value; out i64 */
   TXF_OP_BUCKETIZE = 2,  /* :128-130  p0 = float boundaries, p1 = int32* count (device); out i64 */
   TXF_OP_FILL_I64 = 3,   /* :132-133  out i64 = fill(x) */
   TXF_OP_FILL_F32 = 4,   /* :132-133  out f32 = fill(x) */
@@ -359,6 +371,13 @@ TXF_API int txf_map_scale_minmax(const txf_operand* x, const float* minmax_dev, 
  * ------------------------------------------------------------------------------------------ */
 TXF_API int txf_fingerprint64_batch(const int32_t* offsets_dev, const uint8_t* pool_dev, int64_t n, uint64_t* out_dev,
                             txf_stream_t stream);
+
+/* Test hook: keep only the low `bits` (1..119) hash bits of the fingerprints of terms longer than
+ * 15 bytes, on the current device, so that fingerprints collide at will; results must not change,
+ * because every fingerprint match in the global table, the lookup and the decode table is confirmed
+ * on the bytes (the count pass bypasses its shared-memory cache for long terms while bits < 119).
+ * 119 restores the default. */
+TXF_API int txf_debug_set_identity_bits(int bits);
 
 /* number of kernels launched by this library in the calling process (bench.py gpu_launches) */
 TXF_API int64_t txf_launch_count(void);

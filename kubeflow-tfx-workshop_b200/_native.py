@@ -96,8 +96,9 @@ _SIGNATURES = {
     "txf_vocab_lookup_bytes": (c_size_t, [c_int64]),
     "txf_vocab_sort_scratch_bytes": (c_size_t, [c_int64]),
     "txf_vocab_local_codes": (c_int64, []),
+    "txf_debug_set_identity_bits": (c_int, [c_int]),
     "txf_vocab_count": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p]),
-    "txf_vocab_final_codes": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_void_p, c_void_p]),
+    "txf_vocab_final_codes": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int64, c_void_p, c_void_p]),
     "txf_vocab_compact": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "txf_vocab_export_meta": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "txf_vocab_export_bytes": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p]),

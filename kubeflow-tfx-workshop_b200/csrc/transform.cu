@@ -103,14 +103,21 @@ __device__ __forceinline__ uint64_t mod_u64(uint64_t x, uint64_t d) {
   return r;
 }
 __device__ __forceinline__ long long vocab1(const uint8_t* str, uint32_t len, const LookupSlot* __restrict__ lut,
-                                            uint64_t mask, long long vocab_size, long long num_oov, long long dflt) {
+                                            uint64_t mask, const uint8_t* __restrict__ lut_pool, long long vocab_size, long long num_oov,
+                                            long long dflt) {
   const StrKey key = make_key(str, len);
+  const bool fp = key_is_fingerprint(key.b);
   uint64_t idx = home_slot(key.a, key.b, mask);
   for (uint64_t probe = 0; probe <= mask; ++probe, idx = (idx + 1) & mask) {
     const LookupSlot* s = lut + idx;
     const unsigned long long sb = s->b;
     if (sb == 0) break;
-    if (sb == key.b && s->a == key.a) return s->id;
+    if (sb != key.b || s->a != key.a) continue;
+    if (fp) {  // a fingerprint hit is confirmed on the vocabulary's bytes
+      const unsigned long long ref = s->strref;
+      if (static_cast<uint32_t>(ref & 0xFFFFFFu) != len || !term_bytes_equal(lut_pool + (ref >> 24), str, len)) continue;
+    }
+    return s->id;
   }
   if (num_oov <= 0) return dflt;
   // out of vocabulary: TF's StringToHashBucketFast = Fingerprint64(term) mod num_oov_buckets
@@ -201,6 +208,7 @@ __device__ __forceinline__ void run_vocab(const XfOp& op, const uint8_t* smem, u
   const LookupSlot* lut = op.smem_off >= 0 ? reinterpret_cast<const LookupSlot*>(smem + op.smem_off)
                                             : static_cast<const LookupSlot*>(op.p0);
   const uint64_t mask = static_cast<uint64_t>(op.a0 - 1);
+  const uint8_t* __restrict__ lut_pool = static_cast<const uint8_t*>(op.p1);
   const long long vocab_size = op.a1, num_oov = op.a2, dflt = op.a3;
   long long* out = static_cast<long long*>(op.out);
   StrTilePipe pipe;
@@ -223,7 +231,7 @@ __device__ __forceinline__ void run_vocab(const XfOp& op, const uint8_t* smem, u
       if (row < r1) {
         int32_t b = __ldg(off + row), e = __ldg(off + row + 1);
         bool v = row_valid(valid, row);
-        __stcs(out + row, vocab1(base + b, v ? static_cast<uint32_t>(e - b) : 0u, lut, mask, vocab_size, num_oov, dflt));
+        __stcs(out + row, vocab1(base + b, v ? static_cast<uint32_t>(e - b) : 0u, lut, mask, lut_pool, vocab_size, num_oov, dflt));
       }
     }
     __syncthreads();  // buffer free: refill it with the tile after next
@@ -250,7 +258,7 @@ __global__ void __launch_bounds__(kXfBlock, 1) transform_strings_kernel(const __
     if (op.smem_off < 0) continue;
     unsigned long long* dst = reinterpret_cast<unsigned long long*>(smem + op.smem_off);
     const unsigned long long* src = static_cast<const unsigned long long*>(op.p0);
-    for (int64_t i = threadIdx.x; i < op.a0 * 3; i += kXfBlock) dst[i] = src[i];
+    for (int64_t i = threadIdx.x; i < op.a0 * static_cast<int64_t>(sizeof(LookupSlot) / 8); i += kXfBlock) dst[i] = src[i];
   }
   __syncthreads();
   for (int o = 0; o < nops; ++o) run_vocab(s_ops[o], smem, smem + prog.stage_off, n);
@@ -413,6 +421,11 @@ __global__ void __launch_bounds__(kTileThreads) transform_tiles_kernel(const __g
 
 static int g_last_grid = 0, g_last_block = 0, g_last_smem = 0;
 
+int transform_set_identity_mask(unsigned long long ma, unsigned long long mb) {
+  TXF_CUDA(set_identity_mask_this_tu(ma, mb));
+  return TXF_OK;
+}
+
 }  // namespace txf
 
 extern "C" {
@@ -447,7 +460,8 @@ int txf_transform(const txf_op* ops, int nops, int64_t n, txf_stream_t stream) {
         break;
       }
       case TXF_OP_VOCAB: {
-        TXF_REQUIRE(s.p0 != nullptr && s.pool != nullptr, "transform: op %d (vocabulary) needs lookup table and pool", o);
+        TXF_REQUIRE(s.p0 != nullptr && s.p1 != nullptr && s.pool != nullptr,
+                    "transform: op %d (vocabulary) needs the lookup table (p0), the vocabulary's byte pool (p1) and the column's pool", o);
         TXF_REQUIRE(s.a0 >= 2 && (s.a0 & (s.a0 - 1)) == 0, "transform: op %d lookup capacity must be a power of two", o);
         TXF_REQUIRE(aligned(s.p0, 8), "transform: op %d lookup table not 8B aligned", o);
         have_vocab = true;

@@ -7,9 +7,14 @@
 // (vocab.cuh: the bytes themselves up to 15 bytes, a double hash beyond) and is counted in a
 // per-CTA shared-memory table (2048 slots) after one warp-level aggregation round; terms that do
 // not fit go straight to the global open-addressing table (32-byte slots, one DRAM sector per
-// probe), into which the front tables are flushed at the end.  Counts are exact.  The
-// first thread to claim a slot copies the term's bytes into an arena, so the table is
-// self-contained: it can be exchanged between ranks and outlives the chunk it was built from.
+// probe), into which the front tables are flushed at the end.  Terms of up to 15 bytes are their
+// own key.  Longer terms carry a fingerprint (119 hash bits + the exact length): the global table --
+// which every count reaches, through a flush, a direct add or a merge between ranks -- confirms every
+// fingerprint match on the BYTES against its arena, so two terms never share a global slot; a CTA's
+// front table is a cache in front of it that trusts the full fingerprint for the rows of one CTA.
+// The thread that claims a global slot copies the term's bytes into the arena before it publishes
+// the slot, so the table is self-contained: it can be exchanged between ranks and outlives the
+// chunk it was built from.
 // Ranking reproduces tft: drop '' and terms containing \n / \r, order by (count, bytes)
 // descending, keep top_k.
 // Algorithmic bytes of the count pass: 4 (offset) + term bytes per row + 1 validity bit.
@@ -18,7 +23,10 @@
 
 namespace txf {
 
-constexpr int kVcWarps = 32;
+#ifndef TXF_VC_WARPS
+#define TXF_VC_WARPS 32
+#endif
+constexpr int kVcWarps = TXF_VC_WARPS;
 constexpr int kVcBlock = kVcWarps * 32;   // ONE persistent CTA per SM; its warps run independent pipelines (no block barriers)
 constexpr int kVcSlots = 2048;            // shared-memory front table of the CTA: 2048 x 24 B = 48 KB
 constexpr int kVcProbes = 8;
@@ -37,40 +45,76 @@ __device__ __forceinline__ unsigned long long ldcg64(const unsigned long long* p
   return __ldcg(p);  // L2 only: never a stale L1 line for words other SMs update atomically
 }
 
+constexpr uint64_t kMaxProbes = 1u << 14;
+constexpr uint32_t kSpinLimit = 1u << 22;  // a claimed slot is published within a few hundred cycles; this only bounds a bug
+
+// the 8 bytes at p (any alignment) read with L2-only loads: arena lines are written by other SMs
+// while this kernel runs, and a line may sit in this SM's L1 from before its neighbour term was added
+__device__ __forceinline__ uint64_t fetch64_cg(const uint8_t* p) {
+  const uintptr_t a = reinterpret_cast<uintptr_t>(p);
+  const unsigned long long* q = reinterpret_cast<const unsigned long long*>(a & ~static_cast<uintptr_t>(7));
+  const uint32_t sh = static_cast<uint32_t>(a & 7) * 8;
+  const uint64_t lo = __ldcg(q), hi = __ldcg(q + 1);
+  return (lo >> sh) | ((hi << 1) << (63 - sh));
+}
+__device__ bool arena_term_equals(const uint8_t* arena_term, const uint8_t* str, uint32_t n) {
+  uint32_t i = 0;
+  for (; i + 8 <= n; i += 8)
+    if (fetch64_cg(arena_term + i) != fetch64(str + i)) return false;
+  if (i < n) {
+    const uint64_t m = (1ULL << (8 * (n - i))) - 1;
+    if ((fetch64_cg(arena_term + i) ^ fetch64(str + i)) & m) return false;
+  }
+  return true;
+}
+
 // Add `cnt` occurrences of the term with identity (a, b), whose bytes are str[0..len), to the
-// global table; returns the slot index of the term.  Lock-free and exact: a slot is claimed by CAS on word a, then on word b; a term
-// that finds its a but a different b simply moves on to the next slot.
-__device__ uint32_t table_add(CountSlot* table, uint64_t mask, unsigned long long ka, unsigned long long kb,
+// global table; returns the slot index of the term.  Lock-free and exact.  A slot is claimed by CAS
+// on word a; the claimer copies the term into the arena, stores strref, and only then publishes
+// word b.  Anyone who finds its a waits for b (a few hundred cycles), moves on if b differs, and --
+// for a fingerprint -- compares the bytes with the arena copy and moves on if they differ.
+__device__ __noinline__ uint32_t table_add(CountSlot* table, uint64_t mask, unsigned long long ka, unsigned long long kb,
                               unsigned long long cnt, const uint8_t* str, uint32_t len, uint8_t* arena, int64_t arena_cap,
                               unsigned long long* ctrl) {
+  const bool fp = key_is_fingerprint(kb);
   uint64_t idx = home_slot(ka, kb, mask);
-  for (uint64_t probe = 0; probe <= mask; ++probe, idx = (idx + 1) & mask) {
+  const uint64_t max_probe = mask < kMaxProbes ? mask : kMaxProbes;  // a chain this long means the table is as good as full
+  for (uint64_t probe = 0; probe <= max_probe; ++probe, idx = (idx + 1) & mask) {
     CountSlot* s = table + idx;
     unsigned long long cur = ldcg64(&s->a);
     if (cur == 0) {
       cur = atomicCAS(&s->a, 0ULL, ka);
-      if (cur == 0) { cur = ka; atomicAdd(&ctrl[1], 1ULL); }
+      if (cur == 0) {  // this thread owns the slot: keep the term's bytes, then publish it
+        atomicAdd(&ctrl[1], 1ULL);
+        const unsigned long long off = atomicAdd(&ctrl[0], static_cast<unsigned long long>(len));
+        unsigned long long ref = 0;
+        if (len > kMaxTermLen || off + len > static_cast<unsigned long long>(arena_cap)) {
+          atomicOr(&ctrl[2], 1ULL);
+        } else {
+          for (uint32_t i = 0; i < len; ++i) arena[off + i] = str[i];
+          ref = (off << 24) | len;
+        }
+        __stcg(&s->strref, ref);
+        atomicAdd(&s->count, cnt);
+        __threadfence();
+        atomicExch(&s->b, kb);
+        return static_cast<uint32_t>(idx);
+      }
     }
     if (cur != ka) continue;
     unsigned long long t = ldcg64(&s->b);
-    if (t == 0) {
-      t = atomicCAS(&s->b, 0ULL, kb);
-      if (t == 0) {  // this thread owns the slot: keep the term's bytes
-        t = kb;
-        unsigned long long off = atomicAdd(&ctrl[0], static_cast<unsigned long long>(len));
-        if (len > kMaxTermLen || off + len > static_cast<unsigned long long>(arena_cap)) {
-          atomicOr(&ctrl[2], 1ULL);
-          s->strref = 0;
-        } else {
-          for (uint32_t i = 0; i < len; ++i) arena[off + i] = str[i];
-          s->strref = (off << 24) | len;
-        }
-      }
+    for (uint32_t spin = 0; t == 0; ++spin) {
+      if (spin > kSpinLimit) { atomicOr(&ctrl[2], 32ULL); return 0xFFFFFFFFu; }
+      __nanosleep(32);
+      t = ldcg64(&s->b);
     }
-    if (t == kb) {
-      atomicAdd(&s->count, cnt);
-      return static_cast<uint32_t>(idx);
+    if (t != kb) continue;
+    if (fp) {  // same fingerprint: the bytes decide (ref == 0: the arena overflowed, the pass is void anyway)
+      const unsigned long long ref = ldcg64(&s->strref);
+      if (ref != 0 && (static_cast<uint32_t>(ref & 0xFFFFFFu) != len || !arena_term_equals(arena + (ref >> 24), str, len))) continue;
     }
+    atomicAdd(&s->count, cnt);
+    return static_cast<uint32_t>(idx);
   }
   atomicOr(&ctrl[2], 2ULL);  // table full
   return 0xFFFFFFFFu;
@@ -115,10 +159,12 @@ __device__ __noinline__ int vc_find_slow(unsigned long long* s_a, unsigned long 
 }
 
 // Count one term per lane (has == false: the lane only takes part in the warp votes).  Must be
-// called by all 32 lanes of a warp together.
-__device__ __forceinline__ int vc_count(const VcFront& f, bool has, StrKey key, uint32_t row, int32_t b, uint32_t len) {
+// called by all 32 lanes of a warp together.  use_front == false sends the term straight to the
+// byte-verified global table (test hook: fingerprints truncated on purpose).
+__device__ __forceinline__ int vc_count(const VcFront& f, bool has, StrKey key, uint32_t row, int32_t b, uint32_t len,
+                                        bool use_front = true) {
   int slot = -1;
-  if (has) {
+  if (has && use_front) {
     const uint32_t idx = static_cast<uint32_t>(home_slot(key.a, key.b, kVcSlots - 1));
     // fast path: the term already sits in its home slot (both words are written before any count)
     const unsigned long long a0 = *reinterpret_cast<volatile unsigned long long*>(&f.s_a[idx]);
@@ -192,7 +238,7 @@ __device__ __forceinline__ void vc_issue(const VcSource& src, const VcStage& st,
 // columns that mix empty/short and long terms would otherwise idle most lanes during the hashing.
 template <bool STAGED, bool META>
 __device__ __forceinline__ void vc_step(const VcFront& f, const VcSource& src, const VcStage& st, uint32_t r0, uint32_t r1,
-                                        uint16_t* wqueue, const uint4* s_mask, int& empty_slot) {
+                                        uint16_t* wqueue, const uint4* s_mask, int& empty_slot, bool front_long) {
   const int32_t* soff = st.off();
   const uint8_t* base = STAGED ? st.bytes() - st.a0() : src.pool;       // the term at pool offset o is at base + o
   const uint32_t sbase = STAGED ? smem_u32(st.bytes()) - st.a0() : 0u;
@@ -245,7 +291,7 @@ __device__ __forceinline__ void vc_step(const VcFront& f, const VcSource& src, c
       len = static_cast<uint32_t>((META ? soff[r + 1] : __ldg(src.offsets + row + 1)) - b);
       key = STAGED ? make_key_hashed_smem(sbase + static_cast<uint32_t>(b), len) : make_key_hashed(PtrFetch{base + b}, len);
     }
-    vc_count(f, has, key, row, b, len);
+    vc_count(f, has, key, row, b, len, front_long);
   }
 }
 
@@ -265,6 +311,8 @@ __global__ void __launch_bounds__(kVcBlock, 1) vocab_count_kernel(const int32_t*
   f.s_cnt = reinterpret_cast<uint32_t*>(f.s_b + kVcSlots);
   f.s_row = f.s_cnt + kVcSlots;
   f.table = table; f.mask = mask; f.arena = arena; f.arena_cap = arena_cap; f.ctrl = ctrl; f.codes = codes; f.pool = pool;
+  // test hook: with fingerprints truncated on purpose the front table (which trusts them) is bypassed for long terms
+  const bool front_long = identity_mask(1) == kFpBitsB && identity_mask(0) == ~0ULL;
   for (int i = threadIdx.x; i < kVcSlots; i += kVcBlock) { f.s_a[i] = 0; f.s_b[i] = 0; f.s_cnt[i] = 0; f.s_row[i] = 0; }
   const int warp = threadIdx.x >> 5;
   uint8_t* wbase = reinterpret_cast<uint8_t*>(f.s_row + kVcSlots) + static_cast<size_t>(warp) * kVcWarpBytes;
@@ -295,9 +343,11 @@ __global__ void __launch_bounds__(kVcBlock, 1) vocab_count_kernel(const int32_t*
     const uint32_t r0 = t * kVcStepRows, r1 = step_end(t);
     mbar_wait(&bars[s], (k >> 1) & 1u);
     const VcStage st{wbase + s * kVcStageBytes};
-    if (st.staged() && st.meta()) vc_step<true, true>(f, src, st, r0, r1, wqueue, s_mask, empty_slot);
-    else if (st.staged()) vc_step<true, false>(f, src, st, r0, r1, wqueue, s_mask, empty_slot);
-    else vc_step<false, false>(f, src, st, r0, r1, wqueue, s_mask, empty_slot);
+    // two instantiations only (the kernel is issue-bound and its code must stay in the instruction cache): the
+    // staged one for full, aligned steps; everything else (ragged last step, oversized or misaligned spans) reads
+    // offsets and bytes from global memory
+    if (st.staged() && st.meta()) vc_step<true, true>(f, src, st, r0, r1, wqueue, s_mask, empty_slot, front_long);
+    else vc_step<false, false>(f, src, st, r0, r1, wqueue, s_mask, empty_slot, front_long);
     __syncwarp();  // every lane is done with the stage: refill it with the step after next
     const uint32_t nxt = t + 2 * nw;
     if (lane_id() == 0 && nxt < nsteps) vc_issue(src, st, &bars[s], nxt * kVcStepRows, step_end(nxt));
@@ -339,7 +389,8 @@ __global__ void vocab_export_blob_kernel(const CountSlot* __restrict__ table, co
                                          int64_t K, int64_t S, unsigned long long* __restrict__ sec) {
   const int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
   const unsigned long long kept = ctrl[3];
-  if (i == 0) atomicOr(&sec[0], kept);  // caller zeroes word 0; bit 62 may be OR-ed in concurrently
+  // caller zeroes word 0; bit 62 may be OR-ed in concurrently; bits 56..61 = this rank's own overflow flags (ctrl[2])
+  if (i == 0) atomicOr(&sec[0], kept | ((ctrl[2] & 0x3FULL) << 56));
   if (i >= K || static_cast<unsigned long long>(i) >= kept) return;
   const CountSlot s = table[ent[i]];
   const uint32_t len = static_cast<uint32_t>(s.strref & 0xFFFFFFu);
@@ -362,8 +413,9 @@ __global__ void vocab_insert_blob_kernel(const unsigned long long* __restrict__ 
   const int64_t i = idx % K;
   const unsigned long long* sec = blob + r * stride_words + sec_off;
   const unsigned long long head = sec[0];
-  const unsigned long long kept = head & ((1ULL << 62) - 1);
-  if (i == 0 && (kept > static_cast<unsigned long long>(K) || (head >> 62))) atomicOr(&ctrl[2], 4ULL);  // section overflowed
+  const unsigned long long kept = head & ((1ULL << 56) - 1);
+  if (i == 0 && (kept > static_cast<unsigned long long>(K) || ((head >> 62) & 1))) atomicOr(&ctrl[2], 4ULL);  // section overflowed
+  if (i == 0 && ((head >> 56) & 0x3FULL)) atomicOr(&ctrl[2], 64ULL | (((head >> 56) & 0x3FULL) << 8));  // a rank's local pass overflowed
   if (static_cast<unsigned long long>(i) >= kept) return;
   const uint32_t len = static_cast<uint32_t>(sec[1 + 3 * K + i]);
   if (len > S) return;
@@ -403,6 +455,7 @@ __global__ void vocab_compact_kernel(const CountSlot* __restrict__ table, int64_
   if (occ && keep) {
     ent[kp] = static_cast<uint32_t>(i);
     counts[kp] = cnt > 0xFFFFFFFFULL ? 0xFFFFFFFFu : static_cast<uint32_t>(cnt);
+    if (cnt > 0xFFFFFFFFULL) atomicOr(&ctrl[2], 16ULL);  // the top-k cut-off is selected on 32-bit counts: refuse, never mis-rank
   } else if (occ) {
     ent[capacity - 1 - dp] = static_cast<uint32_t>(i);
   }
@@ -502,12 +555,16 @@ __global__ void vocab_sort_unpad_kernel(const uint32_t* __restrict__ buf, int64_
   if (i < m) ent[i] = buf[i];
 }
 
-__device__ void lookup_put(LookupSlot* lut, uint64_t mask, unsigned long long ka, unsigned long long kb, int32_t id) {
+// Every vocabulary entry gets a slot of its own (entries are distinct terms); strref points at the
+// entry's bytes so that a fingerprint hit can be confirmed by whoever looks a term up.
+__device__ void lookup_put(LookupSlot* lut, uint64_t mask, unsigned long long ka, unsigned long long kb, unsigned long long strref,
+                           int32_t id) {
   uint64_t idx = home_slot(ka, kb, mask);
   for (uint64_t probe = 0; probe <= mask; ++probe, idx = (idx + 1) & mask) {
     unsigned long long cur = atomicCAS(&lut[idx].b, 0ULL, kb);  // b is never 0: it marks occupancy
     if (cur == 0) {
       lut[idx].a = ka;
+      lut[idx].strref = strref;
       lut[idx].id = id;
       return;
     }
@@ -519,15 +576,16 @@ __global__ void vocab_build_lookup_kernel(const CountSlot* __restrict__ table, c
   int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
   if (i >= k) return;
   CountSlot s = table[ent[i]];
-  lookup_put(lut, mask, s.a, s.b, static_cast<int32_t>(i));
+  lookup_put(lut, mask, s.a, s.b, s.strref, static_cast<int32_t>(i));
 }
 
 __global__ void vocab_lookup_from_terms_kernel(const int32_t* __restrict__ offsets, const uint8_t* __restrict__ pool,
                                                int64_t k, LookupSlot* lut, uint64_t mask) {
   int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
   if (i >= k) return;
-  StrKey key = make_key(pool + offsets[i], static_cast<uint32_t>(offsets[i + 1] - offsets[i]));
-  lookup_put(lut, mask, key.a, key.b, static_cast<int32_t>(i));
+  const uint32_t len = static_cast<uint32_t>(offsets[i + 1] - offsets[i]);
+  StrKey key = make_key(pool + offsets[i], len);
+  lookup_put(lut, mask, key.a, key.b, (static_cast<unsigned long long>(offsets[i]) << 24) | (len & 0xFFFFFFu), static_cast<int32_t>(i));
 }
 
 // Dictionary decode table: for every code the count pass may have written (front-table slots of
@@ -535,31 +593,39 @@ __global__ void vocab_lookup_from_terms_kernel(const int32_t* __restrict__ offse
 // vocabulary id, or vocab_size + Fingerprint64(term) % num_oov_buckets, or default_value.
 __global__ void vocab_final_codes_kernel(const CountSlot* __restrict__ table, int64_t capacity,
                                          const uint8_t* __restrict__ arena, const uint32_t* __restrict__ local2global,
-                                         const LookupSlot* __restrict__ lut, uint64_t lmask, long long vocab_size,
-                                         long long num_oov, long long dflt, long long* __restrict__ final_code) {
+                                         const LookupSlot* __restrict__ lut, uint64_t lmask, const uint8_t* __restrict__ lut_pool,
+                                         long long vocab_size, long long num_oov, long long dflt, long long* __restrict__ final_code) {
   int64_t code = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
   if (code >= static_cast<int64_t>(kVcLocalCodes) + capacity) return;
   uint32_t g = code < kVcLocalCodes ? local2global[code] : static_cast<uint32_t>(code - kVcLocalCodes);
   if (g == 0xFFFFFFFFu || g >= capacity) return;
   CountSlot s = table[g];
   if (s.a == 0 || s.b == 0) return;
+  const uint8_t* str = arena + (s.strref >> 24);
+  const uint32_t len = static_cast<uint32_t>(s.strref & 0xFFFFFFu);
+  const bool fp = key_is_fingerprint(s.b);
   long long id = -1;
   uint64_t idx = home_slot(s.a, s.b, lmask);
   for (uint64_t probe = 0; probe <= lmask; ++probe, idx = (idx + 1) & lmask) {
     const LookupSlot l = lut[idx];
     if (l.b == 0) break;
-    if (l.b == s.b && l.a == s.a) { id = l.id; break; }
+    if (l.b != s.b || l.a != s.a) continue;
+    if (fp && (static_cast<uint32_t>(l.strref & 0xFFFFFFu) != len || !term_bytes_equal(lut_pool + (l.strref >> 24), str, len))) continue;
+    id = l.id;
+    break;
   }
   if (id < 0) {
     if (num_oov > 0) {
-      uint64_t fp = fingerprint64(arena + (s.strref >> 24), static_cast<uint32_t>(s.strref & 0xFFFFFFu));
-      id = vocab_size + static_cast<long long>(fp % static_cast<uint64_t>(num_oov));
+      uint64_t h = fingerprint64(str, len);
+      id = vocab_size + static_cast<long long>(h % static_cast<uint64_t>(num_oov));
     } else {
       id = dflt;
     }
   }
   final_code[code] = id;
 }
+
+int transform_set_identity_mask(unsigned long long ma, unsigned long long mb);  // transform.cu's copy of the test-hook masks
 
 static bool pow2(int64_t x) { return x > 0 && (x & (x - 1)) == 0; }
 static int64_t next_pow2(int64_t x) { int64_t p = 1; while (p < x) p <<= 1; return p; }
@@ -574,6 +640,15 @@ size_t txf_vocab_lookup_bytes(int64_t lookup_cap) { return lookup_cap > 0 ? stat
 size_t txf_vocab_sort_scratch_bytes(int64_t m) { return m > 0 ? static_cast<size_t>(txf::next_pow2(m)) * sizeof(uint32_t) : 0; }
 
 int64_t txf_vocab_local_codes(void) { return txf::kVcLocalCodes; }
+
+int txf_debug_set_identity_bits(int bits) {
+  using namespace txf;
+  TXF_REQUIRE(bits >= 1 && bits <= 119, "debug_set_identity_bits: bits=%d out of [1,119]", bits);
+  const unsigned long long ma = bits >= 64 ? ~0ULL : (1ULL << bits) - 1;
+  const unsigned long long mb = bits <= 64 ? 0ULL : (1ULL << (bits - 64)) - 1;
+  TXF_CUDA(set_identity_mask_this_tu(ma, mb));
+  return transform_set_identity_mask(ma, mb);
+}
 
 int txf_vocab_count(const int32_t* offsets_dev, const uint8_t* pool_dev, const uint8_t* valid_dev, int64_t n, void* table_dev,
                     int64_t capacity, uint8_t* arena_dev, int64_t arena_cap, uint64_t* ctrl_dev, uint32_t* codes_dev,
@@ -600,16 +675,17 @@ int txf_vocab_count(const int32_t* offsets_dev, const uint8_t* pool_dev, const u
 }
 
 int txf_vocab_final_codes(const void* table_dev, int64_t capacity, const uint8_t* arena_dev, const uint32_t* local2global_dev,
-                          const void* lookup_dev, int64_t lookup_cap, int64_t vocab_size, int64_t num_oov_buckets,
-                          int64_t default_value, int64_t* final_code_dev, txf_stream_t stream) {
+                          const void* lookup_dev, int64_t lookup_cap, const uint8_t* lookup_pool_dev, int64_t vocab_size,
+                          int64_t num_oov_buckets, int64_t default_value, int64_t* final_code_dev, txf_stream_t stream) {
   using namespace txf;
   TXF_REQUIRE(pow2(capacity) && capacity < (1LL << 31), "vocab_final_codes: capacity must be a power of two below 2^31");
   TXF_REQUIRE(pow2(lookup_cap), "vocab_final_codes: lookup_cap must be a power of two");
-  TXF_REQUIRE(table_dev && arena_dev && local2global_dev && lookup_dev && final_code_dev, "vocab_final_codes: null pointer");
+  TXF_REQUIRE(table_dev && arena_dev && local2global_dev && lookup_dev && lookup_pool_dev && final_code_dev,
+              "vocab_final_codes: null pointer");
   int64_t total = static_cast<int64_t>(kVcLocalCodes) + capacity;
   vocab_final_codes_kernel<<<blocks_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const CountSlot*>(table_dev), capacity, arena_dev, local2global_dev, static_cast<const LookupSlot*>(lookup_dev),
-      static_cast<uint64_t>(lookup_cap - 1), vocab_size, num_oov_buckets, default_value,
+      static_cast<uint64_t>(lookup_cap - 1), lookup_pool_dev, vocab_size, num_oov_buckets, default_value,
       reinterpret_cast<long long*>(final_code_dev));
   TXF_LAUNCH_CHECK();
   count_launch(1);

@@ -12,6 +12,7 @@ from __future__ import annotations
 import math
 import os
 import time
+import weakref
 from dataclasses import dataclass, field
 from typing import Dict, List, Optional, Sequence, Tuple, Union
 
@@ -44,12 +45,13 @@ class VocabResult:
     when somebody asks for them (terms(), detach(), save_state): the transform needs the lookup
     table alone, and the export is a handful of launch-bound kernels."""
 
-    def __init__(self, spec_key: Tuple, size: int, lookup: torch.Tensor, lookup_cap: int, terms_offsets: Optional[torch.Tensor] = None,
-                 terms_pool: Optional[torch.Tensor] = None, export=None):
+    def __init__(self, spec_key: Tuple, size: int, lookup: torch.Tensor, lookup_cap: int, lookup_pool: torch.Tensor,
+                 terms_offsets: Optional[torch.Tensor] = None, terms_pool: Optional[torch.Tensor] = None, export=None):
         self.spec_key = spec_key
         self.size = size                      # len(vocabulary) -- the real list length, not top_k
-        self.lookup = lookup                  # uint8 bytes of the 24-byte-slot lookup table
+        self.lookup = lookup                  # uint8 bytes of the 32-byte-slot lookup table
         self.lookup_cap = lookup_cap
+        self.lookup_pool = lookup_pool        # the bytes the table's slots point into (count-table arena or the terms' pool)
         self._offsets, self._pool, self._export = terms_offsets, terms_pool, export
 
     def _materialize(self):
@@ -97,9 +99,9 @@ class TransformState:
     vocabs: Dict[Tuple, VocabResult] = field(default_factory=dict)
     buckets: Dict[int, BucketResult] = field(default_factory=dict)
     num_rows: int = 0
-    # dictionary codes of the analyzed chunks: (vocab key, id(table)) -> (codes int32[n], decode int64[...]).
-    # They alias Engine workspaces and only serve Engine.transform on the very tables that were analyzed.
-    codes: Dict[Tuple, Tuple[torch.Tensor, torch.Tensor]] = field(default_factory=dict)
+    # dictionary codes of the analyzed chunks: (vocab key, chunk index) -> CodedChunk.  They alias Engine
+    # workspaces and only serve Engine.transform on the very tables (same object, same buffers) that were analyzed.
+    codes: Dict[Tuple, "CodedChunk"] = field(default_factory=dict)
     minmax_keys: List[str] = field(default_factory=list)
     minmax: Optional[torch.Tensor] = None                # float32 [n, 2] (min, max) (device)
 
@@ -121,11 +123,43 @@ class TransformState:
         c = lambda t: None if t is None else t.clone()
         return TransformState(
             plan=self.plan, moment_keys=list(self.moment_keys), mean_var=c(self.mean_var), moments=c(self.moments),
-            vocabs={k: VocabResult(v.spec_key, v.size, v.lookup.clone(), v.lookup_cap, v.terms_offsets.clone(), v.terms_pool.clone())
+            vocabs={k: vocab_from_device_terms(v.spec_key, v.size, v.terms_offsets.clone(), v.terms_pool.clone())
                     for k, v in self.vocabs.items()},
             buckets={k: BucketResult(list(b.keys), b.num_buckets, b.boundaries.clone(), b.nbound.clone(), b.path)
                      for k, b in self.buckets.items()},
             num_rows=self.num_rows, minmax_keys=list(self.minmax_keys), minmax=c(self.minmax))
+
+
+@dataclass
+class CodedChunk:
+    """Dictionary codes of one analyzed chunk.  The chunk is remembered by a weak reference plus the
+    addresses and sizes of the source column's buffers: `id()` of a freed table can be reused by
+    another table of the same length, and a column can be replaced on the table after analyze."""
+
+    table: "weakref.ref"
+    offsets_ptr: int
+    pool_ptr: int
+    valid_ptr: Optional[int]
+    n: int
+    codes: torch.Tensor       # int32 [n]
+    decode: torch.Tensor      # int64 [local codes + capacity]
+
+    def matches(self, table: Table, col: StringColumn) -> bool:
+        return (self.table() is table and len(table) == self.n and col.offsets.data_ptr() == self.offsets_ptr
+                and col.pool.data_ptr() == self.pool_ptr and _ptr(col.valid) == self.valid_ptr and self.codes.numel() == self.n)
+
+
+def vocab_from_device_terms(spec_key: Tuple, k: int, offsets: torch.Tensor, pool: torch.Tensor, lookup: Optional[torch.Tensor] = None,
+                            lookup_cap: Optional[int] = None) -> VocabResult:
+    """Self-contained VocabResult over an explicit vocabulary (device int32 offsets [k+1] + byte pool with slack):
+    the lookup table's slots point into `pool`."""
+    if lookup is None:
+        lookup_cap = _pow2_at_least(max(2 * k, 2))
+        lookup = torch.empty(nat.query("txf_vocab_lookup_bytes", lookup_cap), dtype=torch.uint8, device=offsets.device)
+    with torch.cuda.device(offsets.device):
+        nat.call("txf_vocab_lookup_from_terms", offsets.data_ptr(), pool.data_ptr(), k, lookup.data_ptr(), lookup_cap,
+                 torch.cuda.current_stream().cuda_stream)
+    return VocabResult(spec_key, k, lookup, lookup_cap, pool, offsets, pool)
 
 
 AS_STRING_SUFFIX = "@as_string"  # vocabulary over tf.as_string(int64 feature)
@@ -137,6 +171,14 @@ def _vocab_key(s) -> Tuple:
     return (src, s.top_k, s.frequency_threshold)
 
 
+class _VocabGrow(Exception):
+    """Raised (by every rank alike) when a vocabulary pass ran out of table slots or arena bytes."""
+
+    def __init__(self, key: str, what: str, factor: int):
+        super().__init__(f"{key}: {what}")
+        self.key, self.what, self.factor = key, what, factor
+
+
 class Engine:
     def __init__(self, plan: Plan, device: Union[str, torch.device] = "cuda", comm: Optional[Comm] = None,
                  vocab_capacity: int = 1 << 16, arena_bytes: int = 1 << 22, sample_size: int = 1 << 20,
@@ -146,8 +188,10 @@ class Engine:
         if self.device.type != "cuda":
             raise RuntimeError("Engine needs a CUDA device: the analyze/transform kernels have no CPU path")
         self.comm = comm or Comm()
-        self.vocab_capacity = _pow2_at_least(vocab_capacity)
+        self.vocab_capacity = _pow2_at_least(vocab_capacity)   # starting sizes: analyze() grows them when a pass overflows
         self.arena_bytes = int(arena_bytes)
+        self.max_vocab_capacity, self.max_arena_bytes = 1 << 30, 1 << 34
+        self.grow_events: List[Tuple] = []
         self.sample_size = int(sample_size)
         self.bracket_sigmas = float(bracket_sigmas)
         self.seed = int(seed)
@@ -246,9 +290,28 @@ class Engine:
 
     # ---- analyze ------------------------------------------------------------------------------
     def analyze(self, data: Union[Table, Sequence[Table]]) -> TransformState:
+        """One analyze pass.  The vocabulary count table and its byte arena start small; a pass that
+        fills either grows it and runs again (tft has no such knob), on every rank alike."""
         chunks = [data] if isinstance(data, Table) else list(data)
         for c in chunks:
             self._check_table(c)
+        while True:
+            try:
+                return self._analyze_once(chunks)
+            except _VocabGrow as g:
+                if g.what == "table":
+                    if self.vocab_capacity >= self.max_vocab_capacity:
+                        raise nat.NativeError(f"vocabulary of {g.key!r} needs more than {self.max_vocab_capacity} table slots") from None
+                    self.vocab_capacity = min(self.vocab_capacity * g.factor, self.max_vocab_capacity)
+                else:
+                    if self.arena_bytes >= self.max_arena_bytes:
+                        raise nat.NativeError(f"vocabulary of {g.key!r} needs more than {self.max_arena_bytes} arena bytes") from None
+                    self.arena_bytes = min(self.arena_bytes * g.factor, self.max_arena_bytes)
+                self.grow_events.append((g.key, g.what, self.vocab_capacity if g.what == "table" else self.arena_bytes))
+                for k in [k for k in self._ws if k[0].startswith("v_")]:
+                    del self._ws[k]  # table / arena / code buffers are sized by the old capacity
+
+    def _analyze_once(self, chunks: List[Table]) -> TransformState:
         n_local = sum(len(c) for c in chunks)
         if self._profile:
             torch.cuda.synchronize(self.device)
@@ -596,6 +659,7 @@ class Engine:
         for vk, p in voc:
             sizes.append(torch.tensor([p["kept_local"]], dtype=torch.int64, device=dev))
             sizes.append(p["export"][3][-1:].clone())  # bytes of the exported terms
+            sizes.append(p["ctrl"][2:3].clone())       # this rank's overflow flags: every rank must take the same decision
         if not sizes:
             return
         self._tick("x_export")
@@ -605,7 +669,10 @@ class Engine:
         for vk, p in voc:
             kepts = all_sizes[:, k].tolist()
             nbytes = all_sizes[:, k + 1].tolist()
-            k += 2
+            p["peer_flags"] = 0
+            for fl in all_sizes[:, k + 2].tolist():
+                p["peer_flags"] |= int(fl) & 0x3F
+            k += 3
             fp, tg, cnt, offsets, pool = p["export"]
             kmax, bmax = max(max(kepts), 1), (max(max(nbytes), 1) + 7) // 8 * 8  # rows of the gathered matrix stay 8-byte aligned
             lens = torch.zeros(kmax, dtype=torch.int64, device=dev)
@@ -674,7 +741,7 @@ class Engine:
     # -- vocabulary
     def _vocab_bufs(self, tag: str, capacity: int):
         table = self._buf(f"{tag}_table", nat.query("txf_vocab_table_bytes", capacity), torch.uint8, zero=True)
-        arena = self._buf(f"{tag}_arena", self.arena_bytes, torch.uint8)
+        arena = self._buf(f"{tag}_arena", self.arena_bytes + nat.TXF_POOL_SLACK, torch.uint8)  # slack: 8-byte window reads past a term
         ctrl = self._buf(f"{tag}_ctrl", 8, torch.int64, zero=True)
         ent = self._buf(f"{tag}_ent", capacity, torch.int32)
         counts = self._buf(f"{tag}_counts", capacity, torch.int32)
@@ -695,20 +762,24 @@ class Engine:
             l2g = self._buf(f"{tag}_l2g{i}", nlocal, torch.int32)
             nat.call("txf_vocab_count", col.offsets.data_ptr(), col.pool.data_ptr(), _ptr(col.valid), len(ch), table.data_ptr(),
                      cap, arena.data_ptr(), self.arena_bytes, ctrl.data_ptr(), codes.data_ptr(), l2g.data_ptr(), s)
-            coded.append((i, id(ch), codes, l2g))
+            coded.append((i, ch, col, codes, l2g))
         nat.call("txf_vocab_compact", table.data_ptr(), cap, arena.data_ptr(), ent.data_ptr(), counts.data_ptr(), ctrl.data_ptr(), s)
         return dict(tag=tag, cap=cap, table=table, arena=arena, ctrl=ctrl, ent=ent, counts=counts, coded=coded)
 
-    def _check_vocab_ctrl(self, ctrl_host, spec: VocabSpec):
-        if int(ctrl_host[2]) & 2:
-            raise nat.NativeError(
-                f"vocabulary table for {spec.in_key!r} is full ({self.vocab_capacity} slots): raise Engine(vocab_capacity=...)")
-        if int(ctrl_host[2]) & 1:
-            raise nat.NativeError(
-                f"vocabulary arena for {spec.in_key!r} is full ({self.arena_bytes} bytes): raise Engine(arena_bytes=...)")
-        if int(ctrl_host[1]) * 4 > self.vocab_capacity * 3:
-            raise nat.NativeError(
-                f"vocabulary table for {spec.in_key!r} is over 75% full: raise Engine(vocab_capacity=...)")
+    def _check_vocab_flags(self, flags: int, slots_used: Optional[int], spec: VocabSpec):
+        """flags: OR of ctrl[2] of every table involved (the same value on every rank); slots_used: of this
+        rank's table when it alone decides (single rank).  Grow-and-retry, or an error nothing can fix."""
+        key = spec.in_key
+        if flags & 2:
+            raise _VocabGrow(key, "table", 8)
+        if flags & 1:
+            raise _VocabGrow(key, "arena", 8)
+        if slots_used is not None and slots_used * 4 > self.vocab_capacity * 3:
+            raise _VocabGrow(key, "table", 2)  # over 75 % full: probe chains get long
+        if flags & 16:
+            raise nat.NativeError(f"vocabulary of {key!r}: a term occurs more than 2^32-1 times; the top-k cut-off is selected on 32-bit counts")
+        if flags & 32:
+            raise nat.NativeError(f"vocabulary of {key!r}: a claimed table slot was never published (internal error)")
 
     def _export_entries(self, pend, ent: torch.Tensor, m: int):
         """(fp, tag, count, offsets int64 [m+1], pool) of the m listed entries, on the device."""
@@ -732,26 +803,31 @@ class Engine:
         """Per analyzed chunk: code -> final id table, from this rank's OWN count table and the final lookup."""
         s = self._stream()
         nlocal = nat.query("txf_vocab_local_codes")
-        for i, table_id, codes, l2g in local["coded"]:
+        for i, ch, col, codes, l2g in local["coded"]:
             final = self._buf(f"{local['tag']}_final{i}", nlocal + local["cap"], torch.int64)
             nat.call("txf_vocab_final_codes", local["table"].data_ptr(), local["cap"], local["arena"].data_ptr(), l2g.data_ptr(),
-                     res.lookup.data_ptr(), res.lookup_cap, res.size, spec.num_oov_buckets, spec.default_value, final.data_ptr(), s)
-            state.codes[(vk, table_id)] = (codes, final)
+                     res.lookup.data_ptr(), res.lookup_cap, res.lookup_pool.data_ptr(), res.size, spec.num_oov_buckets,
+                     spec.default_value, final.data_ptr(), s)
+            state.codes[(vk, i)] = CodedChunk(weakref.ref(ch), col.offsets.data_ptr(), col.pool.data_ptr(), _ptr(col.valid), len(ch),
+                                              codes, final)
 
     def _vocab_finish(self, vk: Tuple, spec: VocabSpec, pend) -> VocabResult:
         s = self._stream()
         ctrl_host = pend["ctrl"].cpu().tolist()
-        self._check_vocab_ctrl(ctrl_host, spec)
         kept = int(ctrl_host[3])
-        if self.comm.active:
-            ctrl_host = pend["merged"]["ctrl"].cpu().tolist()
-            if int(ctrl_host[2]) & 4:  # fixed-layout section overflowed on some rank (same flag everywhere): sized exchange
+        if not self.comm.active:
+            self._check_vocab_flags(int(ctrl_host[2]), int(ctrl_host[1]), spec)
+        else:
+            # every decision below is taken on values that are identical on all ranks: the merged table's
+            # flags, which carry the OR of every rank's local flags (bit 6, detail in bits 8..13)
+            m = int(pend["merged"]["ctrl"][2].item())
+            self._check_vocab_flags((((m >> 8) & 0x3F) | pend.get("peer_flags", 0)) & ~4, None, spec)  # some rank's local pass
+            if m & 4:  # a fixed-layout section overflowed on some rank: sized exchange
                 self._exchange({}, {vk: pend})
-                ctrl_host = pend["merged"]["ctrl"].cpu().tolist()
+            ctrl_m = pend["merged"]["ctrl"].cpu().tolist()
+            self._check_vocab_flags(int(ctrl_m[2]) & 0x3F & ~4, None, spec)                            # the merged table
             pend = pend["merged"]  # every rank's admitted entries, re-counted into one table
-            if int(ctrl_host[2]):
-                raise nat.NativeError(f"merged vocabulary table/arena for {spec.in_key!r} overflowed")
-            kept = int(ctrl_host[3])
+            kept = int(ctrl_m[3])
         tag, table, arena, ctrl, ent, counts = (pend[k] for k in ("tag", "table", "arena", "ctrl", "ent", "counts"))
         k = kept if spec.top_k is None else min(spec.top_k, kept)
         if spec.frequency_threshold and kept:
@@ -787,18 +863,12 @@ class Engine:
             _, _, _, offsets, pool = self._export_entries(pend, sel, k)
             return offsets.to(torch.int32), pool
 
-        return VocabResult(vk, k, lookup, lookup_cap, export=export)
+        return VocabResult(vk, k, lookup, lookup_cap, arena, export=export)
 
     def _vocab_from_terms(self, vk: Tuple, terms: List[bytes], lookup: Optional[torch.Tensor] = None,
                           lookup_cap: Optional[int] = None) -> VocabResult:
         col = StringColumn.from_list(terms).to(self.device)
-        k = len(terms)
-        if lookup is None:
-            lookup_cap = _pow2_at_least(max(2 * k, 2))
-            lookup = torch.empty(nat.query("txf_vocab_lookup_bytes", lookup_cap), dtype=torch.uint8, device=self.device)
-        nat.call("txf_vocab_lookup_from_terms", col.offsets.data_ptr(), col.pool.data_ptr(), k, lookup.data_ptr(), lookup_cap,
-                 self._stream())
-        return VocabResult(vk, k, lookup, lookup_cap, col.offsets, col.pool)
+        return vocab_from_device_terms(vk, len(terms), col.offsets, col.pool, lookup, lookup_cap)
 
     # ---- transform ----------------------------------------------------------------------------
     def _static_vocab(self, spec: StaticVocabSpec) -> VocabResult:
@@ -874,19 +944,21 @@ class Engine:
                     res = self._static_vocab(spec)
                 else:
                     res = state.vocabs[_vocab_key(spec)]
-                    coded = state.codes.get((_vocab_key(spec), id(table)))
+                    col = self._vocab_source(table, spec)
                     first = next(sp for sp in self.plan.of(VocabSpec) if _vocab_key(sp) == _vocab_key(spec))
-                    if (coded is not None and coded[0].numel() == n and self.use_codes
-                            and (first.num_oov_buckets, first.default_value) == (spec.num_oov_buckets, spec.default_value)):
+                    coded = None
+                    if self.use_codes and (first.num_oov_buckets, first.default_value) == (spec.num_oov_buckets, spec.default_value):
+                        coded = next((c for (vk, _), c in state.codes.items() if vk == _vocab_key(spec) and c.matches(table, col)), None)
+                    if coded is not None:
                         op.kind = nat.OP_VOCAB_CODED  # this very table was analyzed: decode its dictionary codes
-                        op.in0, op.p0 = coded[0].data_ptr(), coded[1].data_ptr()
+                        op.in0, op.p0 = coded.codes.data_ptr(), coded.decode.data_ptr()
                         op.out = o.data_ptr()
                         cols[spec.out_key] = NumericColumn(o)
                         continue
-                    col = self._vocab_source(table, spec)
                 op.kind = nat.OP_VOCAB
                 op.in0, op.valid0, op.pool = col.offsets.data_ptr(), _ptr(col.valid), col.pool.data_ptr()
-                op.p0, op.a0, op.a1, op.a2, op.a3 = res.lookup.data_ptr(), res.lookup_cap, res.size, spec.num_oov_buckets, spec.default_value
+                op.p0, op.p1 = res.lookup.data_ptr(), res.lookup_pool.data_ptr()
+                op.a0, op.a1, op.a2, op.a3 = res.lookup_cap, res.size, spec.num_oov_buckets, spec.default_value
                 cols[spec.out_key] = NumericColumn(o)
             elif isinstance(spec, FillSpec):
                 if col.kind == "string":

@@ -88,3 +88,65 @@ def zscore_close(got, want, mean, var):
     std = float(np.sqrt(np.float32(var))) or 1.0
     atol = 4 * float(np.spacing(np.float32(abs(mean)) + np.float32(1))) / std
     return np.allclose(got, want, rtol=1e-6, atol=atol, equal_nan=True)
+
+
+# ---- Python model of the long-term fingerprint mixer (csrc/vocab.cuh KeyMixer), used to construct
+# adversarial inputs: a window that zeroes one factor of each lane.
+_M32 = 0xFFFFFFFF
+
+
+class KeyMixerModel:
+    """`fold=True`: the current mixer (x*y + (x<<32|y)); `fold=False`: the round-1 mixer (bare product),
+    whose lanes collapse to zero when a factor is zero."""
+
+    def __init__(self, n, fold=True):
+        self.a1 = (n * 0x9E3779B1 + 0x7F4A7C15) & _M32
+        self.b1 = (n ^ 0x632BE5AB) & _M32
+        self.a2 = ((n ^ 0xD6E8FEB8) * 0xC2B2AE3D) & _M32
+        self.b2 = (n + 0x27D4EB2F) & _M32
+        self.fold = fold
+
+    def _mul(self, x, y):
+        p = x * y + (((x << 32) | y) if self.fold else 0)
+        return p & 0xFFFFFFFFFFFFFFFF
+
+    def zeroing_window(self):
+        """8 bytes that make x == 0 in both lanes for the current state."""
+        lo = self.a1 ^ 0x53C5CA59
+        hi = self.a2 ^ 0xA0761D65
+        return (lo | (hi << 32)).to_bytes(8, "little")
+
+    def add(self, w8: bytes):
+        w = int.from_bytes(w8, "little")
+        lo, hi = w & _M32, w >> 32
+        p = self._mul(self.a1 ^ lo ^ 0x53C5CA59, self.b1 ^ hi ^ 0x74743C1B)
+        q = self._mul(self.a2 ^ hi ^ 0xA0761D65, self.b2 ^ lo ^ 0xE7037ED1)
+        self.a1, self.b1, self.a2, self.b2 = p & _M32, p >> 32, q & _M32, q >> 32
+
+    def state(self):
+        return (self.a1, self.b1, self.a2, self.b2)
+
+
+def lane_zeroing_pair(n=32):
+    """Two different n-byte terms (n = 32) whose second 8-byte window zeroes one factor of each mixer
+    lane: under a bare-product mixer both reach the all-zero state and share every later window."""
+    assert n == 32
+    terms = []
+    for k in range(256):  # first windows whose zeroing window holds no line break (such terms never enter a vocabulary)
+        first = b"TERM%04d" % k
+        m = KeyMixerModel(n, fold=False)
+        m.add(first)
+        second = m.zeroing_window()
+        if b"\n" in second or b"\r" in second:
+            continue
+        terms.append(first + second + b"tail-16-bytes-xx")
+        if len(terms) == 2:
+            break
+    states = []  # construction check: the round-1 mixer ends in the same state for both
+    for t in terms:
+        m = KeyMixerModel(n, fold=False)
+        for i in range(0, 32, 8):
+            m.add(t[i:i + 8])
+        states.append(m.state())
+    assert states[0] == states[1] and terms[0] != terms[1]
+    return terms

@@ -172,6 +172,37 @@ def test_coded_and_string_vocabulary_paths_agree(ktw, fn):
         assert np.array_equal(plain[k].values.cpu().numpy(), want[k]), k
 
 
+def test_codes_of_a_freed_table_are_never_applied_to_another_table(ktw, fn):
+    """The dictionary-code path is tied to the analyzed table itself (object and buffers), not to
+    its `id()`: analyze A, free it, transform a same-length B (CPython may hand B the same id),
+    and transform A again after one of its string columns was replaced."""
+    import gc
+    from kubeflow_tfx_workshop_b200 import synth
+    n = 50_000
+    eng = ktw.Engine(ktw.trace(fn, synth.TAXI_SCHEMA))
+    host_a = synth.taxi_table(n, row0=0, backend="numpy")
+    host_b = synth.taxi_table(n, row0=1_000_000, backend="numpy")
+    a = host_a.to("cuda")
+    state = eng.analyze(a)
+    want_a, wstate = O.analyze_and_transform(helpers.oracle_from_table(host_a))
+    want_b = O.transform(helpers.oracle_from_table(host_b), wstate)
+    for _ in range(4):  # several allocations: one of them is likely to reuse A's address
+        del a
+        gc.collect()
+        b = host_b.to("cuda")
+        got = eng.transform(b, state)
+        for k in ("payment_type_xf", "company_xf"):
+            assert np.array_equal(got[k].values.cpu().numpy(), want_b[k]), k
+        a = b
+    # same table object, one string column replaced after analyze: its codes must not be used
+    a = host_a.to("cuda")
+    state = eng.analyze(a)
+    a.columns["company"] = host_b.to("cuda")["company"]
+    got = eng.transform(a, state)
+    assert np.array_equal(got["company_xf"].values.cpu().numpy(), want_b["company_xf"])
+    assert np.array_equal(got["payment_type_xf"].values.cpu().numpy(), want_a["payment_type_xf"])
+
+
 def test_synthetic_generators_agree_on_gpu(ktw):
     """torch-on-GPU generator == numpy twin, bit for bit (the benchmark relies on it)."""
     from kubeflow_tfx_workshop_b200 import synth
@@ -324,6 +355,87 @@ def test_vocabulary_stress(ktw, n_distinct, top_k, oov):
     assert got_vocab == want_vocab, next((i, a, b) for i, (a, b) in enumerate(zip(got_vocab, want_vocab)) if a != b)
     want_ids = O.apply_vocabulary(filled, want_vocab, oov)
     assert np.array_equal(out["s_id"].values.cpu().numpy(), want_ids)
+
+
+def _vocab_roundtrip(ktw, items, top_k, oov, **engine_kw):
+    """analyze+transform of one string column on the GPU (coded path and string path) -> (vocabulary, ids, ids of a
+    re-application to a second table holding the same rows plus terms never analyzed, their oracle ids)."""
+    col = O.StrCol.from_list(items)
+    host = helpers.table_from_oracle({"s": col}, ktw)
+    eng = ktw.Engine(ktw.trace(_vocab_fn(ktw, "s", top_k, oov), host.schema()), **engine_kw)
+    dev = host.to("cuda")
+    out, state = eng.analyze_and_transform(dev)
+    filled = O.fill_in_missing(col)
+    want_vocab = O.finalize_vocabulary(O.vocab_counts(filled), top_k=top_k)
+    got_vocab = state.vocabs[("s", top_k, None)].terms()
+    assert got_vocab == want_vocab, next((i, a, b) for i, (a, b) in enumerate(zip(got_vocab, want_vocab)) if a != b)
+    want_ids = O.apply_vocabulary(filled, want_vocab, oov)
+    assert np.array_equal(out["s_id"].values.cpu().numpy(), want_ids)                         # dictionary-code path
+    eng.use_codes = False
+    assert np.array_equal(eng.transform(dev, state)["s_id"].values.cpu().numpy(), want_ids)    # string path
+    return eng, state, want_vocab
+
+
+def test_terms_that_collided_under_the_round1_mixer_are_distinct(ktw):
+    """Two 32-byte terms whose second window zeroes a factor of each fingerprint lane shared one
+    identity under a bare-product mixer; they must be counted and numbered separately."""
+    a, b = helpers.lane_zeroing_pair()
+    items = [a] * 700 + [b] * 300 + [b"Cash"] * 50 + [None] * 20 + [a[:31]] * 5 + [b + b"x"] * 3
+    rng = np.random.default_rng(3)
+    rng.shuffle(items)
+    _, state, vocab = _vocab_roundtrip(ktw, items, 1000, 10)
+    assert vocab[:3] == [a, b, b"Cash"]
+
+
+@pytest.mark.parametrize("bits", [1, 6, 20])
+def test_fingerprint_collisions_never_merge_terms(ktw, bits):
+    """Test hook txf_debug_set_identity_bits: with only `bits` hash bits kept, long terms collide all
+    over every table (front table, count table, id lookup, decode table); every match is confirmed on
+    the bytes, so vocabulary, counts (through the ranking), ids and OOV ids must equal the oracle's."""
+    nat = ktw._native
+    rng = np.random.default_rng(100 + bits)
+    # long terms of every window class (16..32, 33..64, > 64), many of equal length; short terms; missing cells
+    terms = []
+    for L in (16, 17, 24, 24, 24, 31, 32, 32, 33, 40, 40, 64, 64, 65, 100, 130):
+        terms += [bytes(rng.integers(32, 127, L, dtype=np.uint8)) for _ in range(120)]
+    terms += [b"a" * L for L in (16, 20, 24, 32, 33, 48, 64, 65, 80)]          # equal windows, different lengths
+    terms += [b"Cash", b"Credit Card", b"x" * 15]
+    terms = list(dict.fromkeys(terms))
+    counts = np.maximum(1, 3000 // (np.arange(len(terms)) + 1)).astype(np.int64)
+    counts[400:460] = 7                                                          # a run of ties decided by the bytes
+    rows = np.repeat(np.arange(len(terms)), counts)
+    rng.shuffle(rows)
+    items = [terms[i] for i in rows]
+    for i in rng.integers(0, len(items), len(items) // 10):
+        items[i] = None
+    nat.call("txf_debug_set_identity_bits", bits)
+    try:
+        eng, state, vocab = _vocab_roundtrip(ktw, items, 1000, 10)
+        # re-application to rows never analyzed (TransformDataset): unseen long terms that share fingerprints with
+        # vocabulary terms must come out as OOV ids, never as vocabulary ids
+        unseen = [bytes(rng.integers(32, 127, L, dtype=np.uint8)) for L in (16, 24, 32, 40, 64, 100) for _ in range(300)]
+        items2 = unseen + items[:5000]
+        col2 = O.StrCol.from_list(items2)
+        got2 = eng.transform(helpers.table_from_oracle({"s": col2}, ktw).to("cuda"), state)["s_id"].values.cpu().numpy()
+        assert np.array_equal(got2, O.apply_vocabulary(O.fill_in_missing(col2), vocab, 10))
+        # a detached / reloaded state points its lookup table at its own copy of the terms
+        det = state.detach()
+        got3 = eng.transform(helpers.table_from_oracle({"s": col2}, ktw).to("cuda"), det)["s_id"].values.cpu().numpy()
+        assert np.array_equal(got3, got2)
+    finally:
+        nat.call("txf_debug_set_identity_bits", 119)
+
+
+def test_vocabulary_tables_grow_instead_of_raising(ktw):
+    """Default Engine sizes (65 536 slots, 4 MB of term bytes) are a starting point: a column with more
+    distinct terms / bytes grows the table and the arena and runs the pass again (tft has no such knob)."""
+    rng = np.random.default_rng(11)
+    n = 150_000
+    items = [b"%06d-%s" % (i, bytes(rng.integers(97, 123, 30, dtype=np.uint8))) for i in range(n)]  # 37 bytes each: 5.5 MB
+    items += items[:2000] * 3
+    eng, state, vocab = _vocab_roundtrip(ktw, items, 1000, 10)
+    assert eng.vocab_capacity >= 1 << 18 and eng.arena_bytes > 1 << 22 and len(eng.grow_events) >= 2
+    assert len(vocab) == 1000
 
 
 @pytest.mark.parametrize("top_k,thr", [(None, 3), (1000, 5), (10, 2), (None, 10 ** 9), (50, 1)])

@@ -191,6 +191,10 @@ int main(int argc, char** argv) {
     # identity corner cases: NUL padding, a leading 8-byte word of zeros, prefixes of each other
     items += [b"", b"\0", b"\0\0", b"\0" * 8, b"\0" * 9, b"\0" * 15, b"\0" * 16, b"\x01", b"ab", b"ab\0", b"ab\0\0",
               b"abcdefgh", b"abcdefgh\0", b"abcdefghi", b"Credit Card", b"Credit Cash", b"x" * 15, b"x" * 16, b"x" * 17]
+    # two 32-byte terms whose second window zeroes a factor of each mixer lane (they collided under a bare-product mixer)
+    items += helpers.lane_zeroing_pair()
+    # same windows, different lengths: the length is part of a long term's key
+    items += [b"a" * 20, b"a" * 24, b"a" * 33, b"a" * 64, b"a" * 65, b"a" * 127, b"a" * 128, b"a" * 129]
     blob = b"".join(len(s).to_bytes(4, "little") + s for s in items)
     (tmp_path / "in.bin").write_bytes(blob)
     out = subprocess.run([str(exe), str(tmp_path / "in.bin")], capture_output=True, text=True, check=True).stdout.split("\n")
@@ -208,6 +212,79 @@ int main(int argc, char** argv) {
     probes = np.array([-1.5, -0.0, 0.0, 1e-45, 2.0], np.float32)
     assert [int(k[1]) for k in keys] == O.order_key(probes).tolist()
     assert [int(k[2], 16) for k in keys] == O.key_to_f32(O.order_key(probes)).view(np.uint32).tolist()
+
+
+def test_long_term_fingerprint_quality(tmp_path):
+    """Avalanche and slice-collision statistics of the long-term fingerprint (vocab.cuh KeyMixer), on the
+    host build of the header.  The fingerprint only pre-filters (matches are confirmed on the bytes), so
+    this guards speed, not correctness: every input bit must flip every kept output bit with
+    probability near 1/2, and 32-bit slices must collide about as often as random values do."""
+    src = tmp_path / "mixer.cu"
+    src.write_text(r'''
+#include <cstdio>
+#include <cstring>
+#include <cstdint>
+#include <vector>
+#include <algorithm>
+#include "common.cuh"
+#include "farmhash.cuh"
+#include "vocab.cuh"
+namespace txf { void set_error(const char*, ...) {} int check_cuda(cudaError_t, const char*) { return 0; } void count_launch(int) {} }
+static uint64_t rng_state = 88172645463325252ULL;
+static uint64_t rnd() { rng_state ^= rng_state << 13; rng_state ^= rng_state >> 7; rng_state ^= rng_state << 17; return rng_state; }
+int main() {
+  const int lens[] = {16, 17, 24, 31, 32, 33, 40, 64, 65, 100};
+  double lo = 1.0, hi = 0.0;
+  for (int n : lens) {
+    std::vector<uint32_t> flips(static_cast<size_t>(n) * 8 * 119, 0);
+    const int trials = 3000;
+    std::vector<unsigned char> buf(n + 64, 0);
+    for (int t = 0; t < trials; ++t) {
+      for (int i = 0; i < n; ++i) buf[i] = static_cast<unsigned char>(rnd());
+      const txf::StrKey k0 = txf::make_key(buf.data(), n);
+      for (int bit = 0; bit < n * 8; ++bit) {
+        buf[bit >> 3] ^= 1u << (bit & 7);
+        const txf::StrKey k1 = txf::make_key(buf.data(), n);
+        buf[bit >> 3] ^= 1u << (bit & 7);
+        const uint64_t da = k0.a ^ k1.a, db = (k0.b ^ k1.b) & ((1ULL << 55) - 1);
+        uint32_t* f = &flips[static_cast<size_t>(bit) * 119];
+        for (int o = 0; o < 64; ++o) f[o] += (da >> o) & 1;
+        for (int o = 0; o < 55; ++o) f[64 + o] += (db >> o) & 1;
+      }
+    }
+    for (uint32_t c : flips) { const double p = static_cast<double>(c) / trials; lo = std::min(lo, p); hi = std::max(hi, p); }
+  }
+  printf("AVALANCHE %.4f %.4f\n", lo, hi);
+  // slice collisions over structured names (digits + words, like the synthetic company names)
+  const int N = 1 << 20;
+  std::vector<uint32_t> s0(N), s1(N), s2(N), s3(N);
+  char name[96];
+  for (int i = 0; i < N; ++i) {
+    int n = snprintf(name, sizeof(name), "%04d - %05d Taxi Affiliation Services %d", i % 10000, (i * 7) % 100000, i / 10000);
+    unsigned char b[160] = {0};
+    memcpy(b, name, n);
+    const txf::StrKey k = txf::make_key(b, n);
+    s0[i] = static_cast<uint32_t>(k.a); s1[i] = static_cast<uint32_t>(k.a >> 32);
+    s2[i] = static_cast<uint32_t>(k.b); s3[i] = static_cast<uint32_t>((k.b >> 20) ^ (k.a >> 13));
+  }
+  for (auto* v : {&s0, &s1, &s2, &s3}) {
+    std::sort(v->begin(), v->end());
+    long c = 0;
+    for (int i = 1; i < N; ++i) c += (*v)[i] == (*v)[i - 1];
+    printf("COLLISIONS %ld\n", c);
+  }
+  return 0;
+}
+''')
+    exe = tmp_path / "mixer"
+    csrc = os.path.join(ROOT, "kubeflow-tfx-workshop_b200", "csrc")
+    subprocess.run(["nvcc", "-O2", "-std=c++17", "-I", csrc, "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
+    out = subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split("\n")
+    lo, hi = (float(x) for x in out[0].split()[1:])
+    assert 0.42 <= lo and hi <= 0.58, (lo, hi)   # 3000 trials: sigma = 0.009, ~4e5 (input bit, output bit) cells
+    expected = (1 << 20) ** 2 / 2 ** 33          # birthday estimate for 2^20 values in 2^32 bins = 128
+    for line in out[1:5]:
+        assert int(line.split()[1]) < 1.5 * expected, out
 
 
 def test_shard_range(ktw):

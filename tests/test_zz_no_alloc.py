@@ -11,6 +11,8 @@ import numpy as np
 import pytest
 import torch
 
+from helpers import O
+
 pytestmark = pytest.mark.gpu
 
 
@@ -45,6 +47,14 @@ def test_no_alloc_moments_match_workspace_entry_point_twice():
         # same kernels, same grid, same merge order: the two entry points agree to the last bit
         assert np.array_equal(got, want), (call, got, want)
         assert got[0, 0] == n
+        # and, independently of the other entry point, what the oracle computes for the filled columns
+        present = np.unpackbits(bits.cpu().numpy(), bitorder="little")[:n].astype(bool)
+        for c, (v, m) in enumerate(cols):
+            x = v.cpu().numpy().astype(np.float32)
+            cnt, mean, m2 = O.moments(np.where(present, x, np.float32(0)) if m is not None else x)
+            assert got[c, 0] == cnt
+            assert abs(got[c, 1] - mean) <= 1e-12 * max(abs(mean), 1.0), (call, c)
+            assert abs(got[c, 2] - m2) <= 1e-10 * max(abs(m2), 1.0), (call, c)
     # beyond the built-in scratch: a clear error instead of an allocation
     cols5 = [(torch.zeros(64, device="cuda"), None)] * 5
     with pytest.raises(nat.NativeError, match="at most 4 columns"):
