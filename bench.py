@@ -1,28 +1,41 @@
 #!/usr/bin/env python
 """Benchmark of the hot path: preprocessing_fn analyze + transform rows/s (BASELINE.json metric).
 
-    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
-    python bench.py --impl reference --gpus N --steps K --warmup W   # CPU arm (oracle port, host cores)
+    python bench.py --gpus N --steps K --warmup W                      # this repo's CUDA path (configs[1] per GPU)
+    python bench.py --gpus N --global-rows 1000000000 ...              # configs[2] as written: 1 B rows over N GPUs
+    python bench.py --workload vocab_stress | bucket_stress            # configs[3] / configs[4]
+    python bench.py --impl reference --gpus N --steps K --warmup W     # CPU arm (oracle port, host cores)
 
 For N > 1 launch with `python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py
---gpus N ...` (one rank per GPU, NCCL).  A step is one full analyze+transform pass over the
-synthetic taxi rows already resident in HBM; rank 0 prints ONE JSON line.
+--gpus N ...` (one rank per GPU, NCCL).  A step is one full analyze+transform pass
+(`Engine.analyze_and_transform`, what tft_beam.AnalyzeAndTransformDataset does) over the synthetic
+rows already resident in HBM; rank 0 prints ONE JSON line.  After the timed region the last step is
+verified (`parity_check`): analyzer state identical on every rank, equal to a single-rank
+recomputation over all shards, outputs equal to the oracle's on a deterministic 1/64 of the rows; a
+mismatch makes the run exit non-zero.
 """
 import argparse
+import importlib
+import importlib.util
 import json
 import os
 import subprocess
 import sys
 import threading
 import time
+import types
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
-sys.path.insert(0, os.path.join(ROOT, "tests"))
+# The pass keeps four streams busy at once (main, two analyzer streams, the state-free transform stream).  With the
+# default of 8 host->device work queues two of them can share a queue and serialise falsely (measured: 7.55 ms per
+# step against 6.65 ms); the variable must be set before the CUDA context exists.
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 
 METRIC = "preprocessing_fn analyze+transform rows/sec"
 UNIT = "rows/s"
 ROWS_PER_GPU = 100_000_000  # BASELINE.json configs[1]: 100M synthetic taxi rows on one B200
+CHUNK_ROWS = 100_000_000    # string pools hold < 2^31 bytes: larger shards are lists of chunks
 
 
 def parse_args():
@@ -31,12 +44,19 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="taxi", choices=["taxi", "vocab_stress", "bucket_stress"])
     ap.add_argument("--rows-per-gpu", type=int, default=ROWS_PER_GPU)
-    ap.add_argument("--e2e-rows", type=int, default=0, help="rows per GPU of the end-to-end leg (0 = same as --rows-per-gpu, bounded by host RAM)")
+    ap.add_argument("--global-rows", type=int, default=0, help="total rows sharded over the GPUs (strong scaling; configs[2] = 1e9)")
+    ap.add_argument("--chunk-rows", type=int, default=CHUNK_ROWS)
+    ap.add_argument("--num-buckets", type=int, default=100, help="bucket_stress: num_buckets (10 / 100 / 1000)")
+    ap.add_argument("--e2e-rows", type=int, default=0, help="rows per GPU of the end-to-end leg (0 = same as the shard, bounded by host RAM)")
     ap.add_argument("--e2e-steps", type=int, default=16)
     ap.add_argument("--cpu-rows", type=int, default=6_000_000, help="sample of the workload timed on the host cores")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-parity-check", action="store_true")
+    ap.add_argument("--out-ring", type=int, default=0, help="write the outputs of a multi-chunk shard into this many reused output sets (0 = one set per chunk)")
+    ap.add_argument("--no-overlap", action="store_true", help="time Engine.analyze + Engine.transform back to back instead")
     return ap.parse_args()
 
 
@@ -92,14 +112,44 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------
-# CPU arm: the oracle port on the host cores (reported baseline / --impl reference)
+# CPU arm: the oracle port on the host cores (reported baseline / --impl reference).  It never
+# imports the product package (and so never maps libtaxi_xf.so): the synthetic-data module is loaded
+# under a private package name whose __init__ is not executed.
 # ------------------------------------------------------------------------------------------------
+def _data_modules():
+    """(synth, columns) of the package directory WITHOUT running the package's __init__ (which loads the CUDA library)."""
+    name = "_txf_data"
+    if name not in sys.modules:
+        pkg = types.ModuleType(name)
+        pkg.__path__ = [os.path.join(ROOT, "kubeflow-tfx-workshop_b200")]
+        sys.modules[name] = pkg
+    return importlib.import_module(name + ".synth"), importlib.import_module(name + ".columns")
+
+
+def _oracle():
+    from oracle import tft_oracle as O
+    return O
+
+
+def _oracle_cols(table):
+    """Table (host) -> the oracle's column objects."""
+    O = _oracle()
+    cols = {}
+    for k, c in table.items():
+        if c.kind == "string":
+            off, pool, valid = c.numpy()
+            cols[k] = O.StrCol(off, pool, valid)
+        else:
+            v, valid = c.numpy()
+            cols[k] = O.NumCol(v, valid)
+    return cols
+
+
 def _cpu_partial(args):
     lo, hi = args
-    import helpers
-    from helpers import O
-    from kubeflow_tfx_workshop_b200 import synth
-    cols = helpers.oracle_from_table(synth.taxi_table(hi - lo, lo, backend="numpy"))
+    synth, _ = _data_modules()
+    O = _oracle()
+    cols = _oracle_cols(synth.taxi_table(hi - lo, lo, backend="numpy"))
     t0 = time.perf_counter()
     part = O.analyze_partial(cols)
     return part, time.perf_counter() - t0
@@ -107,10 +157,9 @@ def _cpu_partial(args):
 
 def _cpu_transform(args):
     lo, hi, state = args
-    import helpers
-    from helpers import O
-    from kubeflow_tfx_workshop_b200 import synth
-    cols = helpers.oracle_from_table(synth.taxi_table(hi - lo, lo, backend="numpy"))
+    synth, _ = _data_modules()
+    O = _oracle()
+    cols = _oracle_cols(synth.taxi_table(hi - lo, lo, backend="numpy"))
     t0 = time.perf_counter()
     out = O.transform(cols, state)
     return sum(len(v) for v in out.values()), time.perf_counter() - t0
@@ -120,8 +169,7 @@ def cpu_pass(rows: int, cores: int, pool=None):
     """One analyze+transform pass of the oracle over `rows` synthetic rows, row-sharded over
     `cores` processes, partial analyzer states merged like the GPU ranks do.  Returns seconds of
     the slowest worker per phase + the merge (input generation is not timed, as on the GPU)."""
-    import helpers
-    from helpers import O
+    O = _oracle()
     cuts = [rows * i // cores for i in range(cores + 1)]
     spans = [(a, b) for a, b in zip(cuts, cuts[1:])]
     if pool is None:
@@ -145,8 +193,7 @@ def run_reference(args):
     if rank != 0:
         return
     import multiprocessing as mp
-    from __graft_entry__ import build
-    build()
+    _oracle().build_c()  # gcc: the oracle's bulk FarmHash helper; the CUDA library is neither built nor loaded here
     cores = len(os.sched_getaffinity(0))
     rows = args.cpu_rows * max(1, min(cores, 16) // 2)
     times = []
@@ -162,7 +209,9 @@ def run_reference(args):
         "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32/i64/u8", "data": "synthetic",
         "config": {"workload": "taxi preprocessing_fn analyze+transform, synthetic Chicago-taxi schema", "rows_per_step": rows,
-                   "note": "bounded sample of the 100M-row workload; tft/Beam itself is not installable on this box"},
+                   "note": f"bounded sample ({rows} rows per step) of the 100M-row workload so that the arm ends within minutes; the port's "
+                           "time is linear in rows (row-sharded numpy passes + one merge), so rows/s carries over to 100M rows. "
+                           "tft/Beam itself is not installable on this box"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
                          "sample": f"{rows} synthetic taxi rows per step, row-sharded over {cores} processes"},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -174,8 +223,49 @@ def run_reference(args):
 # ------------------------------------------------------------------------------------------------
 # GPU arm
 # ------------------------------------------------------------------------------------------------
+def _load_example_fn(ktw, name="taxi_preprocessing"):
+    """examples/<name>.py imported with the tf / tft stand-ins bound (the GPU box has no /root/reference)."""
+    with ktw.install_shims():
+        spec = importlib.util.spec_from_file_location(name, os.path.join(ROOT, "examples", name + ".py"))
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+    return mod
+
+
 def table_bytes(table, keys):
     return sum(table[k].nbytes() for k in keys)
+
+
+def _peak():
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        return json.load(open(peaks_path))["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def _workload(args, ktw, synth, dev, rank, world):
+    """-> (plan, chunks, rows_local, description).  Shards are lists of chunks of <= chunk_rows rows."""
+    import torch
+    if args.workload == "taxi":
+        fn = _load_example_fn(ktw).preprocessing_fn
+        plan = ktw.trace(fn, synth.TAXI_SCHEMA)
+        if args.global_rows:
+            lo, hi = ktw.shard_range(args.global_rows, rank, world)
+        else:
+            lo, hi = rank * args.rows_per_gpu, (rank + 1) * args.rows_per_gpu
+        chunks = [synth.taxi_table(min(args.chunk_rows, hi - s), row0=s, backend="torch", device=dev) for s in range(lo, hi, args.chunk_rows)]
+        desc = ("taxi preprocessing_fn analyze+transform on synthetic Chicago-taxi-schema rows "
+                + ("(BASELINE configs[2]: global rows sharded over the GPUs)" if args.global_rows else "(BASELINE configs[1] per GPU)"))
+        return plan, chunks, hi - lo, desc
+    mod = _load_example_fn(ktw, "stress_preprocessing")
+    R = args.rows_per_gpu
+    if args.workload == "vocab_stress":
+        table = synth.vocab_stress_table(R, row0=rank * R, device=dev)
+        plan = ktw.trace(mod.vocab_stress_fn, table.schema())
+        return plan, [table], R, "vocabulary stress (BASELINE configs[3]): 2 string columns, 10M distinct terms, top_k=1000, 10 OOV buckets"
+    table = synth.bucket_stress_table(R, row0=rank * R, device=dev)
+    plan = ktw.trace(mod.bucket_stress_fn(args.num_buckets), table.schema(), dense_keys=set(table.keys()))
+    return plan, [table], R, f"bucketize stress (BASELINE configs[4]): 8 float columns, num_buckets={args.num_buckets}"
 
 
 def run_b200(args):
@@ -196,15 +286,12 @@ def run_b200(args):
         dist.barrier()
     import kubeflow_tfx_workshop_b200 as ktw
     from kubeflow_tfx_workshop_b200 import synth
-    import helpers
     nat = ktw._native
 
-    R = args.rows_per_gpu
-    fn = helpers.load_example_preprocessing_fn(ktw).preprocessing_fn
-    plan = ktw.trace(fn, synth.TAXI_SCHEMA)
+    plan, chunks, R, desc = _workload(args, ktw, synth, dev, rank, world)
     comm = ktw.Comm()
-    eng = ktw.Engine(plan, device=dev, comm=comm)
-    table = synth.taxi_table(R, row0=rank * R, backend="torch", device=dev)
+    big_vocab = args.workload == "vocab_stress"
+    eng = ktw.Engine(plan, device=dev, comm=comm, **({"vocab_capacity": 1 << 25, "arena_bytes": 1 << 29} if big_vocab else {}))
     torch.cuda.synchronize()
 
     def barrier():
@@ -212,59 +299,78 @@ def run_b200(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    def step(out):
+        if args.no_overlap:
+            state = eng.analyze(chunks)
+            return [eng.transform(c, state, o) for c, o in zip(chunks, out)], state
+        return eng.analyze_and_transform(chunks, out)
+
     # warm-up (also allocates every workspace and the output buffers)
-    out = None
+    ring = args.out_ring if 0 < args.out_ring < len(chunks) else 0
+    if ring:  # a shard larger than a chunk writes its outputs into a reused ring of output sets
+        sets, _ = eng.analyze_and_transform(chunks[:ring])
+        out = [sets[i % ring] for i in range(len(chunks))]
+    else:
+        out = [None] * len(chunks)
     for _ in range(max(args.warmup, 3)):
-        state = eng.analyze(table)
-        out = eng.transform(table, state, out)
+        out, state = step(out)
     barrier()
 
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(args.steps)]
     launches0 = nat.launch_count()
     barrier()
     t_start = torch.cuda.Event(enable_timing=True)
     t_end = torch.cuda.Event(enable_timing=True)
     t_start.record()
     for i in range(args.steps):
-        ev[i][0].record()
-        state = eng.analyze(table)
-        ev[i][1].record()
-        out = eng.transform(table, state, out)
-        ev[i][2].record()
+        out, state = step(out)
     t_end.record()
     barrier()
     launches = nat.launch_count() - launches0
     clocks = sampler.stop() if rank == 0 else None
     total_ms = t_start.elapsed_time(t_end)
-    analyze_ms = sum(e[0].elapsed_time(e[1]) for e in ev) / args.steps
-    transform_ms = sum(e[1].elapsed_time(e[2]) for e in ev) / args.steps
-    t = torch.tensor([total_ms, analyze_ms, transform_ms], dtype=torch.float64, device=dev)
+
+    # the two phases on their own (not overlapped), for the roofline of the dominant kernel
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+    reps = 3
+    a_ms = x_ms = 0.0
+    for _ in range(reps):
+        ev[0].record()
+        st2 = eng.analyze(chunks)
+        ev[1].record()
+        out = [eng.transform(c, st2, o) for c, o in zip(chunks, out)]
+        ev[2].record()
+        torch.cuda.synchronize()
+        a_ms += ev[0].elapsed_time(ev[1]) / reps
+        x_ms += ev[1].elapsed_time(ev[2]) / reps
+    out, state = step(out)  # leave the outputs of the timed entry point in place for the parity check
+    torch.cuda.synchronize()
+    t = torch.tensor([total_ms, a_ms, x_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     total_ms, analyze_ms, transform_ms = t.tolist()
     ms_per_step = total_ms / args.steps
-    value = world * R / (ms_per_step * 1e-3)
+    rows_all = torch.tensor([R], dtype=torch.int64, device=dev)
+    if world > 1:
+        dist.all_reduce(rows_all)
+    global_rows = int(rows_all.item())
+    value = global_rows / (ms_per_step * 1e-3)
 
     # roofline of the dominant kernel (the fused transform): algorithmic bytes / measured time
     in_keys = plan.input_keys()
-    read_b = table_bytes(table, in_keys)
-    write_b = sum(out[k].nbytes() for k in out.keys())
-    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
-    if os.path.exists(peaks_path):
-        peak, peak_src = json.load(open(peaks_path))["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs)"
-    else:
-        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    read_b = sum(table_bytes(c, in_keys) for c in chunks)
+    write_b = sum(o[k].nbytes() for o in out for k in o.keys())  # a ring is written once per chunk that maps to it
+    peak, peak_src = _peak()
     xf_gbs = (read_b + write_b) / (transform_ms * 1e-3) / 1e9
-    traffic = None  # dram__bytes_read.sum + dram__bytes_write.sum of one transform launch (ncu --set full capture)
+    traffic = None
     tpath = os.path.join(ROOT, "profiles", "r1_transform_traffic.json")
-    if os.path.exists(tpath):
+    if os.path.exists(tpath) and args.workload == "taxi":
         tj = json.load(open(tpath))
         traffic = (tj["dram_bytes_read"] + tj["dram_bytes_write"]) * (R / tj["rows"])
     analyze_keys = eng.moment_keys + [k for ks in eng.bucket_groups.values() for k in ks] + [s.in_key for s in eng.vocab_specs.values()]
-    analyze_b = table_bytes(table, analyze_keys)
+    analyze_b = sum(table_bytes(c, analyze_keys) for c in chunks)
     whole_gbs = (analyze_b + read_b + write_b) / (ms_per_step * 1e-3) / 1e9
     import ctypes
     g, b, s = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
@@ -272,15 +378,20 @@ def run_b200(args):
 
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong" if args.global_rows else "weak", "vs_baseline": None,
         "dtype": "f32/i64/u8", "data": "synthetic",
-        "config": {"workload": "taxi preprocessing_fn analyze+transform on synthetic Chicago-taxi-schema rows (BASELINE configs[1])",
-                   "rows_per_gpu": R, "global_rows": world * R, "l2": "inputs (%.1f GB per GPU) larger than L2" % (read_b / 1e9),
-                   "quantile_path": eng.last_quantile_path.get(10), "parallelism": f"rows sharded over {world} GPU(s)"},
-        "phases_ms": {"analyze": analyze_ms, "transform": transform_ms},
+        "config": {"workload": desc, "rows_per_gpu": R, "global_rows": global_rows, "chunks_per_gpu": len(chunks),
+                   "l2": "inputs (%.1f GB per GPU) larger than L2" % (read_b / 1e9),
+                   "quantile_path": {str(k): v for k, v in eng.last_quantile_path.items()},
+                   "entry_point": "Engine.analyze + Engine.transform" if args.no_overlap else
+                                  "Engine.analyze_and_transform (state-free ops streamed under the analyzers)",
+                   "parallelism": f"rows sharded over {world} GPU(s)"},
+        "phases_ms": {"analyze_alone": analyze_ms, "transform_alone": transform_ms, "sum_not_overlapped": analyze_ms + transform_ms},
         "roofline": {"bound": "hbm", "kernel": "transform_tiles_kernel", "achieved": xf_gbs, "peak": peak, "unit": "GB/s",
                      "frac": xf_gbs / peak, "traffic": traffic, "peak_source": peak_src,
+                     "traffic_source": None if traffic is None else "constant from one committed ncu --set full capture (profiles/r1_transform_traffic.json), scaled to this row count; not measured by this run",
                      "traffic_frac": None if traffic is None else traffic / (transform_ms * 1e-3) / 1e9 / peak,
+                     "timing": "CUDA events around Engine.transform run alone (all ops in one launch), average of 3",
                      "note": "achieved/frac use SURVEY 8(d) algorithmic bytes, which count the string columns' term bytes; the kernel "
                              "reads 4-byte dictionary codes written by the count pass instead, so its DRAM traffic (traffic, "
                              "traffic_frac) is lower and frac can exceed 1",
@@ -292,12 +403,17 @@ def run_b200(args):
         "clocks": clocks,
     }
 
+    ok = True
+    if not args.no_parity_check:
+        pc = parity_check(args, ktw, synth, eng, plan, chunks, out, state, dev, rank, world)
+        ok = bool(pc["ok"])
+        line["parity_check"] = pc
     # end-to-end: pinned host buffers -> H2D -> analyze+transform -> D2H of every output column
-    if not args.no_e2e:
-        line["e2e"] = run_e2e(args, eng, plan, table, out, dev, world, rank, barrier)
-    del table, out
+    if not args.no_e2e and args.workload == "taxi":
+        line["e2e"] = run_e2e(args, eng, plan, chunks[0], out[0], dev, world, rank, barrier)
+    del chunks, out
     torch.cuda.empty_cache()
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    if rank == 0 and world == 1 and not args.no_cpu_baseline and args.workload == "taxi":
         t0 = time.perf_counter()
         sec = cpu_pass(args.cpu_rows, 1)
         line["cpu_baseline"] = {"value": args.cpu_rows / sec, "unit": UNIT, "cores": 1, "kind": "port",
@@ -308,11 +424,158 @@ def run_b200(args):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+    if not ok:
+        sys.exit(3)
+
+
+# ------------------------------------------------------------------------------------------------
+# parity check of the last step (after the timed region)
+# ------------------------------------------------------------------------------------------------
+def _state_signature(state):
+    """Everything the transform depends on, as bytes: moments, boundaries, vocabulary terms in id order."""
+    import numpy as np
+    parts = []
+    if state.moments is not None:
+        parts.append(state.moments.cpu().numpy().tobytes())
+        parts.append(state.mean_var.cpu().numpy().tobytes())
+    for nb in sorted(state.buckets):
+        res = state.buckets[nb]
+        for k in res.keys:
+            parts.append(res.boundaries_of(k).astype(np.float32).tobytes())
+    for key in sorted(state.vocabs, key=str):
+        terms = state.vocabs[key].terms()
+        parts.append(repr((key, len(terms))).encode())
+        parts.append(b"\x00".join(terms))
+    return parts
+
+
+def _host_rows(table, lo, hi):
+    """Rows [lo, hi) of a device table as a host table (lo % 8 == 0)."""
+    import kubeflow_tfx_workshop_b200 as ktw
+    cols = {}
+    for k, c in table.items():
+        valid = None if c.valid is None else c.valid[lo // 8:(hi + 7) // 8].cpu()
+        if c.kind == "numeric":
+            cols[k] = ktw.NumericColumn(c.values[lo:hi].cpu(), valid)
+        else:
+            off = c.offsets[lo:hi + 1].cpu()
+            b0, b1 = int(off[0]), int(off[-1])
+            pool = c.pool[b0:b1 + 64].cpu().clone()
+            cols[k] = ktw.StringColumn((off - b0).to(off.dtype), pool, valid, b1 - b0)
+    return ktw.Table(cols)
+
+
+def parity_check(args, ktw, synth, eng, plan, chunks, out, state, dev, rank, world):
+    """(1) the analyzer state is bit-identical on every rank; (2) it equals a single-rank recomputation
+    over ALL shards done on rank 0 (vocabulary and boundaries bit-exact, moments to 1e-12) when those
+    rows fit next to the benchmark's buffers; (3) taxi workload: the outputs of this rank equal the
+    oracle's transform (given that state) on a deterministic 1/64 of the rows -- integers and strings
+    bit-exact, z-scores within 1e-6 relative.  Returns a dict for the JSON line."""
+    import hashlib
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    res = {"ok": True}
+    sig = _state_signature(state)
+    digest = hashlib.sha256(b"".join(sig)).digest()
+    d = torch.tensor(list(digest), dtype=torch.uint8, device=dev)
+    if world > 1:
+        g = [torch.empty_like(d) for _ in range(world)]
+        dist.all_gather(g, d)
+        same = all(bool((x == g[0]).all()) for x in g)
+    else:
+        same = True
+    res["state_identical_on_all_ranks"] = same
+    res["state_sha256"] = digest.hex()[:16]
+    res["ok"] &= same
+
+    # (2) single-rank recomputation on rank 0
+    if world > 1 and args.workload == "taxi":
+        total_rows = args.global_rows or world * args.rows_per_gpu
+        need = total_rows * 135  # input bytes + dictionary codes per row
+        free = torch.cuda.mem_get_info(dev)[0]
+        verdict = None
+        if rank == 0:
+            if need < 0.8 * free:
+                spans = [ktw.shard_range(args.global_rows, r, world) if args.global_rows else (r * args.rows_per_gpu, (r + 1) * args.rows_per_gpu)
+                         for r in range(world)]
+                allc = []
+                for lo, hi in spans:
+                    allc += [synth.taxi_table(min(args.chunk_rows, hi - s), row0=s, backend="torch", device=dev) for s in range(lo, hi, args.chunk_rows)]
+                solo = ktw.Engine(plan, device=dev, comm=_NoComm())
+                st1 = solo.analyze(allc)
+                same_vb = all(a == b for a, b in zip(_state_signature(st1)[2:], sig[2:])) and len(_state_signature(st1)) == len(sig)
+                m1, mN = st1.moments.cpu().numpy(), state.moments.cpu().numpy()
+                rel = float(np.max(np.abs(m1 - mN) / np.maximum(np.abs(m1), 1e-300)))
+                verdict = {"rows": total_rows, "vocab_and_boundaries_bit_exact": bool(same_vb), "moments_max_rel_diff": rel,
+                           "ok": bool(same_vb and rel <= 1e-12)}
+                del allc, solo, st1
+                torch.cuda.empty_cache()
+            else:
+                verdict = {"skipped": f"{total_rows} rows need {need / 1e9:.0f} GB on one GPU next to the benchmark's buffers ({free / 1e9:.0f} GB free)", "ok": True}
+        flag = torch.tensor([1 if (verdict is None or verdict["ok"]) else 0], dtype=torch.int32, device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        res["single_rank_recomputation"] = verdict
+        res["ok"] &= bool(flag.item())
+
+    # (3) outputs against the oracle on 1/64 of this rank's rows
+    if args.workload == "taxi":
+        O = _oracle()
+        O.build_c()
+        ostate = {"zscore": {k: tuple(np.float32(v) for v in state.mean_var_of(k)) for k in state.moment_keys},
+                  "vocab": {key[0]: state.vocabs[key].terms() for key in state.vocabs},
+                  "boundaries": {k: res_.boundaries_of(k) for res_ in state.buckets.values() for k in res_.keys}}
+        bad, checked = [], 0
+        live = range(len(chunks)) if not args.out_ring or args.out_ring >= len(chunks) else range(len(chunks) - args.out_ring, len(chunks))
+        for c, o in [(chunks[i], out[i]) for i in live]:  # with an output ring only the last sets still hold their chunk
+            n = len(c)
+            seg = max(8, (n // (64 * 16)) // 8 * 8)
+            for i in range(16):
+                lo = (n * i // 16) // 8 * 8
+                hi = min(lo + seg, n)
+                if hi <= lo:
+                    continue
+                want = O.transform(_oracle_cols(_host_rows(c, lo, hi)), ostate)
+                for key, w in want.items():
+                    col = o[key]
+                    if isinstance(w, list):
+                        off = col.offsets[lo:hi + 1].cpu().numpy()
+                        pool = col.pool[int(off[0]):int(off[-1])].cpu().numpy().tobytes()
+                        got = [pool[a - off[0]:b - off[0]] for a, b in zip(off[:-1], off[1:])]
+                        good = got == w
+                    elif w.dtype == np.float32:
+                        mean, var = ostate["zscore"][key[:-3]]
+                        gotv = col.values[lo:hi].cpu().numpy()
+                        std = float(np.sqrt(np.float32(var))) or 1.0
+                        atol = 4 * float(np.spacing(np.float32(abs(mean)) + np.float32(1))) / std  # x ~ mean is ill-conditioned (SURVEY 7)
+                        good = bool(np.allclose(gotv, w, rtol=1e-6, atol=atol, equal_nan=True))
+                    else:
+                        good = bool(np.array_equal(col.values[lo:hi].cpu().numpy(), w))
+                    if not good:
+                        bad.append(key)
+                checked += hi - lo
+        flag = torch.tensor([0 if bad else 1, checked], dtype=torch.int64, device=dev)
+        if world > 1:
+            g = [torch.empty_like(flag) for _ in range(world)]
+            dist.all_gather(g, flag)
+            allok, checked = all(int(x[0]) for x in g), sum(int(x[1]) for x in g)
+        else:
+            allok = not bad
+        res["outputs_vs_oracle"] = {"rows_checked": int(checked), "mismatching_outputs_rank0": sorted(set(bad)), "ok": bool(allok),
+                                    "tolerance": "integers/strings bit-exact; z-scores rtol 1e-6 + 4 ulp(mean)/std"}
+        res["ok"] &= bool(allok)
+    res["ok"] = bool(res["ok"])
+    return res
+
+
+class _NoComm:
+    """A Comm that is never active: the single-rank recomputation must not talk to the other ranks."""
+    active, enabled, rank, world = False, False, 0, 1
 
 
 def run_e2e(args, eng, plan, table, out, dev, world, rank, barrier):
     """End-to-end leg: every step copies ALL inputs from pinned host memory to the GPU, runs
-    Engine.analyze + Engine.transform (the public API), and copies ALL outputs back to pinned host
+    Engine.analyze_and_transform (the public API), and copies ALL outputs back to pinned host
     memory.  Steps are software-pipelined the way a streaming ingest would run them: two device
     input sets and two device output sets, so step i+1's host->device copy overlaps step i's compute
     and device->host copy (PCIe is full duplex).  The serial (un-pipelined) step time is reported too."""
@@ -321,7 +584,7 @@ def run_e2e(args, eng, plan, table, out, dev, world, rank, barrier):
     import torch.distributed as dist
     import kubeflow_tfx_workshop_b200 as ktw
 
-    R = args.e2e_rows or args.rows_per_gpu
+    R = args.e2e_rows or len(table)
     per_row = (table.nbytes() + sum(out[k].nbytes() for k in out.keys())) / len(table)
     budget = psutil.virtual_memory().available * 0.5 / max(world, 1)
     free_dev = torch.cuda.mem_get_info(dev)[0]
@@ -329,11 +592,11 @@ def run_e2e(args, eng, plan, table, out, dev, world, rank, barrier):
     R -= R % 8
     in_keys = plan.input_keys()
     sub = ktw.Table({k: _slice_col(table[k], R) for k in in_keys})
+    _bind_to_gpu_numa_node(dev)
     host_in = ktw.Table({k: _pin(c) for k, c in sub.items()})
     # device staging buffers and pinned output buffers are allocated once, outside the timed region
     dev_in = [ktw.Table({k: _empty_like(c, dev) for k, c in host_in.items()}) for _ in range(2)]
-    state = eng.analyze(sub)
-    out_dev = [eng.transform(sub, state), eng.transform(sub, state)]
+    out_dev = [eng.analyze_and_transform(sub)[0], eng.analyze_and_transform(sub)[0]]
     host_out = {k: _pinned_like(c) for k, c in out_dev[0].items()}
     h2d = host_in.nbytes()
     d2h = sum(c.nbytes() for c in out_dev[0].columns.values())
@@ -364,8 +627,7 @@ def run_e2e(args, eng, plan, table, out, dev, world, rank, barrier):
                 s_cmp.wait_event(ev_in[b])
                 if ev_out[b] is not None:
                     s_cmp.wait_event(ev_out[b])       # this output set has been read back
-                st = eng.analyze(dev_in[b])
-                o = eng.transform(dev_in[b], st, out_dev[b])
+                o, _ = eng.analyze_and_transform(dev_in[b], out_dev[b])
                 ev_cmp[b] = torch.cuda.Event()
                 ev_cmp[b].record(s_cmp)
             with torch.cuda.stream(s_d2h):
@@ -396,9 +658,37 @@ def run_e2e(args, eng, plan, table, out, dev, world, rank, barrier):
     return {"value": world * R / (piped_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
             "rows_per_gpu": R, "ms_per_step": piped_ms, "steps": args.e2e_steps, "pipelined": True,
             "serial_ms_per_step": serial_ms, "serial_value": world * R / (serial_ms * 1e-3),
+            "copy_gbs_per_gpu_each_way": {"h2d": h2d / (piped_ms * 1e-3) / 1e9, "d2h": d2h / (piped_ms * 1e-3) / 1e9},
+            "host_numa": _NUMA_NOTE.get("note"),
             "timing": "host wall clock around barrier + synchronize (three streams); max over ranks",
-            "api": "Engine.analyze + Engine.transform on tables copied from pinned host memory; every output column copied back; "
+            "api": "Engine.analyze_and_transform on tables copied from pinned host memory; every output column copied back; "
                    "step i+1's upload overlaps step i's compute and download"}
+
+
+_NUMA_NOTE = {}
+
+
+def _bind_to_gpu_numa_node(dev):
+    """Pin this rank's host threads (and so the pages it first-touches and pins) to the CPU cores of the
+    GPU's NUMA node, when the driver reports one: with all ranks on one node the host<->device copies of
+    8 GPUs share that node's memory controllers and inter-socket link."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(dev.index or 0)
+        ncpu = os.cpu_count() or 1
+        words = (ncpu + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = {64 * w + b for w, m in enumerate(mask) for b in range(64) if (m >> b) & 1}
+        allowed = os.sched_getaffinity(0)
+        use = cpus & allowed
+        if use and use != allowed:
+            os.sched_setaffinity(0, use)
+            _NUMA_NOTE["note"] = f"host threads bound to the GPU's {len(use)} local cores before pinning"
+        else:
+            _NUMA_NOTE["note"] = f"GPU's ideal CPU set equals the allowed set ({len(allowed)} cores): nothing to bind"
+    except Exception as e:  # noqa: BLE001 -- optional placement; the copy still works without it
+        _NUMA_NOTE["note"] = f"no NUMA placement ({type(e).__name__})"
 
 
 def _slice_col(c, n):

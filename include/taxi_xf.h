@@ -154,10 +154,13 @@ TXF_API size_t txf_vocab_table_bytes(int64_t capacity);
  * local2global_dev (uint32[txf_vocab_local_codes()]) the table slot behind each CTA-local code;
  * txf_vocab_final_codes turns them into a decode table the fused transform gathers from, so
  * analyze+transform of the SAME rows never re-reads or re-hashes the term bytes. */
+/* cta_warps: 0 or 32 = the count CTA takes a whole SM (fastest alone); 24 = it leaves room for a
+ * txf_transform_stream CTA on the same SM (use when that kernel runs concurrently on another stream). */
 TXF_API int64_t txf_vocab_local_codes(void);
 TXF_API int txf_vocab_count(const int32_t* offsets_dev, const uint8_t* pool_dev, const uint8_t* valid_dev, int64_t n,
                     void* table_dev, int64_t capacity, uint8_t* arena_dev, int64_t arena_cap,
-                    uint64_t* ctrl_dev, uint32_t* codes_dev, uint32_t* local2global_dev, txf_stream_t stream);
+                    uint64_t* ctrl_dev, uint32_t* codes_dev, uint32_t* local2global_dev, int cta_warps,
+                    txf_stream_t stream);
 /* final_code_dev: int64[txf_vocab_local_codes() + capacity]; lookup_dev: the vocabulary's lookup
  * table (txf_vocab_build_lookup / _lookup_from_terms) and lookup_pool_dev the bytes it was built
  * over; semantics of the value = TXF_OP_VOCAB's output for that term */
@@ -246,6 +249,19 @@ typedef struct txf_op {
 } txf_op;
 
 TXF_API int txf_transform(const txf_op* ops, int nops, int64_t n, txf_stream_t stream);
+/* Bytes of a pass-through string feature (TXF_OP_FILL_STR rebases the offsets to 0): out_pool[0 .. m) =
+ * pool[offsets[0] .. offsets[n]), m = offsets[n] - offsets[0] <= max_bytes (the caller's bound on the span,
+ * which only sizes the grid).  out_pool_dev: 8-byte aligned, m bytes + TXF_POOL_SLACK. */
+TXF_API int txf_copy_string_bytes(const int32_t* offsets_dev, const uint8_t* pool_dev, int64_t n, int64_t max_bytes,
+                                  uint8_t* out_pool_dev, txf_stream_t stream);
+/* The ops of a program that need no analyzer result (TXF_OP_FILL_I64 / _F32 / _STR, TXF_OP_RATIO_LABEL;
+ * taxi_utils.py:132-143) as a small-footprint streaming kernel meant to run on a second stream WHILE the
+ * analyzers of the same rows run (tft_beam.AnalyzeAndTransformDataset makes one pass of both,
+ * notebooks/06_Airflow_Feature_Analysis.ipynb:236-262): one 128-thread CTA per SM, 42 KB of shared
+ * memory, tiles moved by the bulk-copy engine.  Same results as txf_transform for these ops; any other
+ * kind is refused.  workspace_dev: txf_transform_stream_workspace_bytes() bytes, used by one call at a time. */
+TXF_API size_t txf_transform_stream_workspace_bytes(void);
+TXF_API int txf_transform_stream(const txf_op* ops, int nops, int64_t n, void* workspace_dev, txf_stream_t stream);
 /* name of the transform kernel and launch geometry of the last call (for profiling notes) */
 TXF_API int txf_transform_launch_info(int* grid, int* block, int* smem_bytes);
 

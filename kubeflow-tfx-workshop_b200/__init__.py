@@ -18,8 +18,13 @@ All arithmetic runs in ``libtaxi_xf.so`` (hand-written sm_100a CUDA behind the C
 from __future__ import annotations
 
 import contextlib
+import os
 import sys
 import types
+
+# analyze_and_transform keeps four CUDA streams busy at once; with the default of 8 host->device work queues two of
+# them can land on one queue and serialise falsely.  Only effective if the CUDA context does not exist yet.
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 
 from . import _native  # noqa: F401  (raises ImportError when libtaxi_xf.so is missing)
 from . import beam_shim as tft_beam

@@ -97,7 +97,7 @@ _SIGNATURES = {
     "txf_vocab_sort_scratch_bytes": (c_size_t, [c_int64]),
     "txf_vocab_local_codes": (c_int64, []),
     "txf_debug_set_identity_bits": (c_int, [c_int]),
-    "txf_vocab_count": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "txf_vocab_count": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     "txf_vocab_final_codes": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int64, c_void_p, c_void_p]),
     "txf_vocab_compact": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "txf_vocab_export_meta": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
@@ -110,6 +110,9 @@ _SIGNATURES = {
     "txf_vocab_build_lookup": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p]),
     "txf_vocab_lookup_from_terms": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p]),
     "txf_transform": (c_int, [POINTER(TxfOp), c_int, c_int64, c_void_p]),
+    "txf_copy_string_bytes": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p]),
+    "txf_transform_stream_workspace_bytes": (c_size_t, []),
+    "txf_transform_stream": (c_int, [POINTER(TxfOp), c_int, c_int64, c_void_p, c_void_p]),
     "txf_transform_launch_info": (c_int, [POINTER(c_int), POINTER(c_int), POINTER(c_int)]),
     "txf_minmax_workspace_bytes": (c_size_t, [c_int]),
     "txf_minmax_begin": (c_int, [c_void_p, c_int, c_void_p]),

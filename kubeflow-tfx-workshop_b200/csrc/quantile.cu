@@ -616,6 +616,9 @@ int txf_qcount(const void* const* values, const uint8_t* const* valid, const int
     TXF_CUDA(cudaFuncSetAttribute(qcount_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
     TXF_CUDA(cudaFuncSetAttribute(qcount_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
   }
+  // same shared-memory split as the other kernels of the pass (a change of split waits for an idle SM)
+  TXF_CUDA(cudaFuncSetAttribute(qcount_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+  TXF_CUDA(cudaFuncSetAttribute(qcount_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
   int per_sm = static_cast<int>((200 * 1024) / (smem + 1024));
   per_sm = per_sm < 1 ? 1 : (per_sm > 6 ? 6 : per_sm);
   dim3 grid(stream_grid(n, kQBlock, per_sm, ncols), ncols);

@@ -419,6 +419,23 @@ __global__ void __launch_bounds__(kTileThreads) transform_tiles_kernel(const __g
   if (tile == 0 && threadIdx.x < (n & 3)) op_row(op, nullptr, (nquads << 2) + threadIdx.x, n);
 }
 
+// Bytes of a pass-through string column: out[0 .. off[n] - off[0]) = pool[off[0] .. off[n]).  The
+// offsets of a sliced column do not start at 0 and the host does not know them without a round trip,
+// so the span is read on the device.  8 bytes per thread and step; the source may be unaligned.
+__global__ void copy_string_bytes_kernel(const int32_t* __restrict__ off, const uint8_t* __restrict__ pool, int64_t n,
+                                         uint8_t* __restrict__ out) {
+  const int64_t b0 = off[0], total = static_cast<int64_t>(off[n]) - b0;
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x * 8;
+  for (int64_t i = (blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x) * 8; i < total; i += stride) {
+    const uint64_t w = fetch64(pool + b0 + i);
+    if (i + 8 <= total) {
+      *reinterpret_cast<uint64_t*>(out + i) = w;
+    } else {
+      for (int k = 0; i + k < total; ++k) out[i + k] = static_cast<uint8_t>(w >> (8 * k));
+    }
+  }
+}
+
 static int g_last_grid = 0, g_last_block = 0, g_last_smem = 0;
 
 int transform_set_identity_mask(unsigned long long ma, unsigned long long mb) {
@@ -525,6 +542,21 @@ int txf_transform(const txf_op* ops, int nops, int64_t n, txf_stream_t stream) {
     count_launch(1);
     if (!tp.prog.nops) { g_last_grid = grid; g_last_block = kXfBlock; g_last_smem = smem; }
   }
+  return TXF_OK;
+}
+
+int txf_copy_string_bytes(const int32_t* offsets_dev, const uint8_t* pool_dev, int64_t n, int64_t max_bytes, uint8_t* out_pool_dev,
+                          txf_stream_t stream) {
+  using namespace txf;
+  TXF_REQUIRE(n >= 0 && n < (1LL << 31) && max_bytes >= 0, "copy_string_bytes: n / max_bytes out of range");
+  if (n == 0 || max_bytes == 0) return TXF_OK;
+  TXF_REQUIRE(offsets_dev && pool_dev && out_pool_dev && aligned(out_pool_dev, 8), "copy_string_bytes: null or misaligned pointer");
+  int64_t blocks = (max_bytes / 8 + 255) / 256;
+  if (blocks < 1) blocks = 1;
+  if (blocks > 8 * kSMs) blocks = 8 * kSMs;
+  copy_string_bytes_kernel<<<static_cast<unsigned>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(offsets_dev, pool_dev, n, out_pool_dev);
+  TXF_LAUNCH_CHECK();
+  count_launch(1);
   return TXF_OK;
 }
 

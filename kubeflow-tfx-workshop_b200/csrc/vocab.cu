@@ -23,11 +23,12 @@
 
 namespace txf {
 
-#ifndef TXF_VC_WARPS
-#define TXF_VC_WARPS 32
-#endif
-constexpr int kVcWarps = TXF_VC_WARPS;
-constexpr int kVcBlock = kVcWarps * 32;   // ONE persistent CTA per SM; its warps run independent pipelines (no block barriers)
+// ONE persistent CTA per SM; its warps run independent pipelines (no block barriers).  Two shapes: 32 warps
+// (the whole SM: 64 registers x 1024 threads, 228 KB of shared memory) when the pass runs alone, and 24 warps
+// (about 185 KB, 72 registers) when the caller streams other work next to it (txf_transform_stream): the count
+// pass is latency-bound per warp (1.94 ms with 32 warps, 2.33 ms with 24 on 100 M taxi rows), the room it gives
+// up lets 12 GB of pass-through bytes move underneath it.
+constexpr int kVcWarpsFull = 32, kVcWarpsShared = 24;
 constexpr int kVcSlots = 2048;            // shared-memory front table of the CTA: 2048 x 24 B = 48 KB
 constexpr int kVcProbes = 8;
 constexpr int kVcStepRows = 96;           // rows per warp and step: three per lane
@@ -36,7 +37,7 @@ constexpr int kVcOffSlots = 100;          // offsets staged per step: 96 + 1, pa
 constexpr int kVcStageCap = 2304;         // staged term bytes per step (24 B per row on average; longer steps read the pool directly)
 constexpr int kVcStageBytes = 16 + kVcOffSlots * 4 + kVcStageCap;  // header | offsets | bytes
 constexpr int kVcWarpBytes = 2 * kVcStageBytes + kVcStepRows * 2;  // two stages + the warp's long-term queue
-constexpr size_t kVcSmemBytes = kVcSlots * (8 + 8 + 4 + 4) + static_cast<size_t>(kVcWarps) * kVcWarpBytes + kVcWarps * 2 * 8;
+constexpr size_t vc_smem_bytes(int warps) { return kVcSlots * (8 + 8 + 4 + 4) + static_cast<size_t>(warps) * kVcWarpBytes + warps * 2 * 8; }
 constexpr uint32_t kPadEnt = 0xFFFFFFFFu;
 constexpr int kVcGrid = kSMs;
 constexpr uint32_t kVcLocalCodes = kVcGrid * kVcSlots;  // codes below this: (CTA, front-table slot); above: global slot
@@ -295,13 +296,16 @@ __device__ __forceinline__ void vc_step(const VcFront& f, const VcSource& src, c
   }
 }
 
-__global__ void __launch_bounds__(kVcBlock, 1) vocab_count_kernel(const int32_t* __restrict__ offsets,
+template <int kVcWarps>
+__global__ void __launch_bounds__(kVcWarps * 32, 1) __maxnreg__(kVcWarps == kVcWarpsFull ? 64 : 72)
+    vocab_count_kernel(const int32_t* __restrict__ offsets,
                                                                   const uint8_t* __restrict__ pool,
                                                                   const uint8_t* __restrict__ valid, int64_t n,
                                                                   CountSlot* table, uint64_t mask, uint8_t* arena,
                                                                   int64_t arena_cap, unsigned long long* ctrl,
                                                                   uint32_t* __restrict__ codes,
                                                                   uint32_t* __restrict__ local2global) {
+  constexpr int kVcBlock = kVcWarps * 32;
   extern __shared__ __align__(16) uint8_t vc_smem[];
   __shared__ uint4 s_mask[16];
   fill_short_masks(s_mask);
@@ -652,9 +656,11 @@ int txf_debug_set_identity_bits(int bits) {
 
 int txf_vocab_count(const int32_t* offsets_dev, const uint8_t* pool_dev, const uint8_t* valid_dev, int64_t n, void* table_dev,
                     int64_t capacity, uint8_t* arena_dev, int64_t arena_cap, uint64_t* ctrl_dev, uint32_t* codes_dev,
-                    uint32_t* local2global_dev, txf_stream_t stream) {
+                    uint32_t* local2global_dev, int cta_warps, txf_stream_t stream) {
   using namespace txf;
   TXF_REQUIRE(n >= 0 && n < (1LL << 31), "vocab_count: n out of range");
+  TXF_REQUIRE(cta_warps == 0 || cta_warps == kVcWarpsFull || cta_warps == kVcWarpsShared, "vocab_count: cta_warps must be 0, %d or %d",
+              kVcWarpsShared, kVcWarpsFull);
   TXF_REQUIRE(pow2(capacity) && capacity < (1LL << 32), "vocab_count: capacity must be a power of two below 2^32");
   TXF_REQUIRE(offsets_dev && pool_dev && table_dev && arena_dev && ctrl_dev && arena_cap > 0, "vocab_count: null pointer");
   TXF_REQUIRE(aligned(table_dev, 32), "vocab_count: table must be 32-byte aligned");
@@ -663,12 +669,20 @@ int txf_vocab_count(const int32_t* offsets_dev, const uint8_t* pool_dev, const u
     TXF_CUDA(cudaMemsetAsync(local2global_dev, 0xFF, static_cast<size_t>(kVcLocalCodes) * sizeof(uint32_t),
                              static_cast<cudaStream_t>(stream)));
   if (n == 0) return TXF_OK;
-  int64_t want = (n + static_cast<int64_t>(kVcStepRows) * kVcWarps - 1) / (static_cast<int64_t>(kVcStepRows) * kVcWarps);
+  const int warps = cta_warps == 0 ? kVcWarpsFull : cta_warps;
+  int64_t want = (n + static_cast<int64_t>(kVcStepRows) * warps - 1) / (static_cast<int64_t>(kVcStepRows) * warps);
   int grid = static_cast<int>(want < kVcGrid ? want : kVcGrid);
-  TXF_CUDA(cudaFuncSetAttribute(vocab_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kVcSmemBytes)));
-  vocab_count_kernel<<<grid, kVcBlock, kVcSmemBytes, static_cast<cudaStream_t>(stream)>>>(
-      offsets_dev, pool_dev, valid_dev, n, static_cast<CountSlot*>(table_dev), static_cast<uint64_t>(capacity - 1), arena_dev,
-      arena_cap, reinterpret_cast<unsigned long long*>(ctrl_dev), codes_dev, local2global_dev);
+  auto launch = [&](auto kernel, int w) -> int {
+    TXF_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(vc_smem_bytes(w))));
+    TXF_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    kernel<<<grid, w * 32, vc_smem_bytes(w), static_cast<cudaStream_t>(stream)>>>(
+        offsets_dev, pool_dev, valid_dev, n, static_cast<CountSlot*>(table_dev), static_cast<uint64_t>(capacity - 1), arena_dev,
+        arena_cap, reinterpret_cast<unsigned long long*>(ctrl_dev), codes_dev, local2global_dev);
+    return TXF_OK;
+  };
+  const int rc = warps == kVcWarpsFull ? launch(vocab_count_kernel<kVcWarpsFull>, kVcWarpsFull)
+                                       : launch(vocab_count_kernel<kVcWarpsShared>, kVcWarpsShared);
+  if (rc) return rc;
   TXF_LAUNCH_CHECK();
   count_launch(1);
   return TXF_OK;

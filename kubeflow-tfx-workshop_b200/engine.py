@@ -192,6 +192,9 @@ class Engine:
         self.arena_bytes = int(arena_bytes)
         self.max_vocab_capacity, self.max_arena_bytes = 1 << 30, 1 << 34
         self.grow_events: List[Tuple] = []
+        self._count_warps = 0        # 24 while analyze_and_transform streams the state-independent ops next to the count pass
+        self.overlap_transform = True  # analyze_and_transform: run the ops that need no analyzer result under the analyzers
+        self._xstream = None
         self.sample_size = int(sample_size)
         self.bracket_sigmas = float(bracket_sigmas)
         self.seed = int(seed)
@@ -761,7 +764,7 @@ class Engine:
             codes = self._buf(f"{tag}_codes{i}", len(ch), torch.int32)
             l2g = self._buf(f"{tag}_l2g{i}", nlocal, torch.int32)
             nat.call("txf_vocab_count", col.offsets.data_ptr(), col.pool.data_ptr(), _ptr(col.valid), len(ch), table.data_ptr(),
-                     cap, arena.data_ptr(), self.arena_bytes, ctrl.data_ptr(), codes.data_ptr(), l2g.data_ptr(), s)
+                     cap, arena.data_ptr(), self.arena_bytes, ctrl.data_ptr(), codes.data_ptr(), l2g.data_ptr(), self._count_warps, s)
             coded.append((i, ch, col, codes, l2g))
         nat.call("txf_vocab_compact", table.data_ptr(), cap, arena.data_ptr(), ent.data_ptr(), counts.data_ptr(), ctrl.data_ptr(), s)
         return dict(tag=tag, cap=cap, table=table, arena=arena, ctrl=ctrl, ent=ent, counts=counts, coded=coded)
@@ -899,24 +902,26 @@ class Engine:
             r.scalar = self._const(float(o[1])).data_ptr()
         return r
 
-    def transform(self, table: Table, state: TransformState, out: Optional[Table] = None) -> Table:
-        """One fused kernel for the ops of the taxi program over one GPU-resident chunk, then one
-        small kernel per sibling mapper (scale, arithmetic, cast) in dependency order; returns the
-        output table (reusing `out`'s buffers when given)."""
-        self._check_table(table)
+    def _run_fused(self, table: Table, state: Optional[TransformState], out: Optional[Table], fused, stream_kernel: bool):
+        """Build the op program of `fused` specs and launch it (txf_transform, or txf_transform_stream for
+        state-free ops); returns {out_key: column}."""
         n = len(table)
         dev = self.device
-        fused = [sp for sp in self.plan.specs if isinstance(sp, (ZScoreSpec, BucketSpec, VocabSpec, StaticVocabSpec, FillSpec,
-                                                                   RatioLabelSpec))]
         ops = (nat.TxfOp * max(len(fused), 1))()
         cols: Dict[str, object] = {}
         copies = []
+        def reuse(prev, dtype):
+            """Buffer of an earlier output column with room for n rows (a ring of output sets may be larger), or a new one."""
+            if prev is not None and prev.values.dtype == dtype and prev.values.numel() >= n:
+                return prev.values[:n]
+            return torch.empty(n, dtype=dtype, device=dev)
+
         for i, spec in enumerate(fused):
             op = ops[i]
-            prev = out[spec.out_key] if out is not None else None
+            prev = out[spec.out_key] if out is not None and spec.out_key in out else None
             if isinstance(spec, RatioLabelSpec):
                 fare, tips = table[spec.fare_key], table[spec.tips_key]
-                o = prev.values if prev is not None else torch.empty(n, dtype=torch.int64, device=dev)
+                o = reuse(prev, torch.int64)
                 op.kind, op.in_dtype = nat.OP_RATIO_LABEL, nat.TXF_F32
                 op.in0, op.valid0, op.in1, op.valid1 = fare.values.data_ptr(), _ptr(fare.valid), tips.values.data_ptr(), _ptr(tips.valid)
                 op.f0 = spec.ratio
@@ -925,7 +930,7 @@ class Engine:
                 continue
             col = table[spec.in_key]
             if isinstance(spec, ZScoreSpec):
-                o = prev.values if prev is not None else torch.empty(n, dtype=torch.float32, device=dev)
+                o = reuse(prev, torch.float32)
                 op.kind, op.in_dtype = nat.OP_ZSCORE, _DT[col.dtype]
                 op.in0, op.valid0 = col.values.data_ptr(), _ptr(col.valid)
                 op.p0 = state.mean_var[state.moment_keys.index(spec.in_key)].data_ptr()
@@ -933,13 +938,13 @@ class Engine:
             elif isinstance(spec, BucketSpec):
                 res = state.buckets[spec.num_buckets]
                 c = res.keys.index(spec.in_key)
-                o = prev.values if prev is not None else torch.empty(n, dtype=torch.int64, device=dev)
+                o = reuse(prev, torch.int64)
                 op.kind, op.in_dtype = nat.OP_BUCKETIZE, _DT[col.dtype]
                 op.in0, op.valid0 = col.values.data_ptr(), _ptr(col.valid)
                 op.p0, op.p1, op.a0 = res.boundaries[c].data_ptr(), res.nbound[c].data_ptr(), res.boundaries.shape[1]
                 cols[spec.out_key] = NumericColumn(o)
             elif isinstance(spec, (VocabSpec, StaticVocabSpec)):
-                o = prev.values if prev is not None else torch.empty(n, dtype=torch.int64, device=dev)
+                o = reuse(prev, torch.int64)
                 if isinstance(spec, StaticVocabSpec):
                     res = self._static_vocab(spec)
                 else:
@@ -962,8 +967,8 @@ class Engine:
                 cols[spec.out_key] = NumericColumn(o)
             elif isinstance(spec, FillSpec):
                 if col.kind == "string":
-                    if prev is not None:
-                        o_off, o_pool = prev.offsets, prev.pool
+                    if prev is not None and prev.offsets.numel() >= n + 1 and prev.pool.numel() >= col.pool_bytes + nat.TXF_POOL_SLACK:
+                        o_off, o_pool = prev.offsets[: n + 1], prev.pool
                     else:
                         o_off = torch.empty(n + 1, dtype=torch.int32, device=dev) if n else torch.zeros(1, dtype=torch.int32, device=dev)
                         o_pool = torch.empty(col.pool_bytes + nat.TXF_POOL_SLACK, dtype=torch.uint8, device=dev)
@@ -973,7 +978,7 @@ class Engine:
                     copies.append((o_pool, col))
                     cols[spec.out_key] = StringColumn(o_off, o_pool, None, col.pool_bytes)
                     continue
-                o = prev.values if prev is not None else torch.empty(n, dtype=col.values.dtype, device=dev)
+                o = reuse(prev, col.values.dtype)
                 op.kind = nat.OP_FILL_F32 if col.dtype == "float32" else nat.OP_FILL_I64
                 op.in_dtype = _DT[col.dtype]
                 op.in0, op.valid0 = col.values.data_ptr(), _ptr(col.valid)
@@ -982,10 +987,42 @@ class Engine:
                 raise AssertionError(spec)
             op.out = o.data_ptr()
         if n and fused:
-            nat.call("txf_transform", ops, len(fused), n, self._stream())
-            for o_pool, col in copies:  # bytes of pass-through string features: plain device copy
-                if col.pool_bytes:
-                    o_pool[: col.pool_bytes].copy_(col.pool[: col.pool_bytes], non_blocking=True)
+            if stream_kernel:
+                ws = self._buf("xstream_ws", nat.query("txf_transform_stream_workspace_bytes"), torch.uint8)
+                nat.call("txf_transform_stream", ops, len(fused), n, ws.data_ptr(), self._stream())
+            else:
+                nat.call("txf_transform", ops, len(fused), n, self._stream())
+            for o_pool, col in copies:  # bytes of pass-through string features (the column may be a slice: its span is read on the device)
+                nat.call("txf_copy_string_bytes", col.offsets.data_ptr(), col.pool.data_ptr(), n, col.pool_bytes, o_pool.data_ptr(),
+                         self._stream())
+        return cols
+
+    @staticmethod
+    def _state_free(spec) -> bool:
+        """Ops that need no analyzer result: fill-missing pass-throughs and the tips label."""
+        return isinstance(spec, (FillSpec, RatioLabelSpec))
+
+    def transform_state_free(self, table: Table, out: Optional[Table] = None) -> Dict[str, object]:
+        """The ops of the program that need no analyzer result, through txf_transform_stream (the
+        small-footprint streaming kernel): queue it on a second stream while `analyze` runs on the same
+        rows, then pass the columns it returns to `transform(..., done=...)`."""
+        self._check_table(table)
+        return self._run_fused(table, None, out, [sp for sp in self.plan.specs if self._state_free(sp)], stream_kernel=True)
+
+    def transform(self, table: Table, state: TransformState, out: Optional[Table] = None,
+                  done: Optional[Dict[str, object]] = None) -> Table:
+        """One fused kernel for the ops of the taxi program over one GPU-resident chunk, then one
+        small kernel per sibling mapper (scale, arithmetic, cast) in dependency order; returns the
+        output table (reusing `out`'s buffers when given).  `done`: output columns already produced by
+        `transform_state_free` for this table; their ops are skipped."""
+        self._check_table(table)
+        n = len(table)
+        dev = self.device
+        done = done or {}
+        fused = [sp for sp in self.plan.specs if isinstance(sp, (ZScoreSpec, BucketSpec, VocabSpec, StaticVocabSpec, FillSpec,
+                                                                   RatioLabelSpec)) and sp.out_key not in done]
+        cols = dict(done)
+        cols.update(self._run_fused(table, state, out, fused, stream_kernel=False))
         # sibling mappers: plan order already has every operand before its user
         made: Dict[str, torch.Tensor] = {k: c.values for k, c in cols.items() if isinstance(c, NumericColumn)}
         for spec in self.plan.specs:
@@ -993,7 +1030,7 @@ class Engine:
                 continue
             prev = out[spec.out_key] if out is not None and spec.out_key in out else None
             dt = torch.int64 if isinstance(spec, CastSpec) and spec.to == "int64" else torch.float32
-            o = prev.values if prev is not None else torch.empty(n, dtype=dt, device=dev)
+            o = prev.values[:n] if prev is not None and prev.values.dtype == dt and prev.values.numel() >= n else torch.empty(n, dtype=dt, device=dev)
             if n:
                 if isinstance(spec, ScaleSpec):
                     x = self._operand(["col", spec.in_key], table, state, made)
@@ -1012,8 +1049,38 @@ class Engine:
         order = [sp.out_key for sp in self.plan.specs if sp.out_key in cols and not sp.out_key.startswith(TEMP_PREFIX)]
         return Table({k: cols[k] for k in order})
 
-    def analyze_and_transform(self, data: Union[Table, Sequence[Table]]):
+    def analyze_and_transform(self, data: Union[Table, Sequence[Table]], out=None):
+        """The single pass tft_beam.AnalyzeAndTransformDataset makes (notebooks/06_...:236-262): analyze the
+        rows and transform the same rows.  The ops that need no analyzer result (pass-throughs, label: half
+        of the transform's bytes) are queued first, on a second stream, as the small-footprint streaming
+        kernel; the analyzers -- issue- and latency-bound, a quarter of the HBM bandwidth -- run next to it
+        (the count pass in its 24-warp shape), and the ops that need their results follow.  `out`: output
+        table(s) of an earlier call whose buffers are reused."""
         chunks = [data] if isinstance(data, Table) else list(data)
-        state = self.analyze(chunks)
-        outs = [self.transform(c, state) for c in chunks]
+        outs_prev = [out] if isinstance(out, Table) else (list(out) if out is not None else [None] * len(chunks))
+        free = [sp for sp in self.plan.specs if self._state_free(sp)]
+        overlap = self.overlap_transform and bool(free) and any(len(c) for c in chunks)
+        done = [None] * len(chunks)
+        if overlap:
+            for c in chunks:
+                self._check_table(c)
+            main = torch.cuda.current_stream()
+            if self._xstream is None:
+                self._xstream = torch.cuda.Stream(device=self.device)
+            xs = self._xstream
+            xs.wait_stream(main)
+            with torch.cuda.stream(xs):
+                done = [self.transform_state_free(c, o) for c, o in zip(chunks, outs_prev)]
+            for d in done:  # buffers allocated under the side stream are handed to the caller's stream
+                for col in d.values():
+                    for t in ((col.values,) if isinstance(col, NumericColumn) else (col.offsets, col.pool)):
+                        t.record_stream(main)
+            self._count_warps = 24
+        try:
+            state = self.analyze(chunks)
+        finally:
+            self._count_warps = 0
+        outs = [self.transform(c, state, o, d) for c, o, d in zip(chunks, outs_prev, done)]
+        if overlap:
+            torch.cuda.current_stream().wait_stream(xs)
         return (outs[0] if isinstance(data, Table) else outs), state

@@ -203,6 +203,46 @@ def test_codes_of_a_freed_table_are_never_applied_to_another_table(ktw, fn):
     assert np.array_equal(got["payment_type_xf"].values.cpu().numpy(), want_a["payment_type_xf"])
 
 
+@pytest.mark.parametrize("n", [1, 7, 1023, 1024, 1025, 2048, 4099, 148 * 4 * 2048 + 13, 3_000_001])
+def test_streamed_state_free_ops_match_fused_kernel(ktw, fn, n):
+    """txf_transform_stream (the small-footprint kernel that runs under the analyzers) against the
+    oracle and against txf_transform, at row counts around its 1024 / 2048-cell tiles, on a table whose
+    string offsets do not start at 0 and whose bitmaps are not 16-byte aligned (slices)."""
+    from kubeflow_tfx_workshop_b200 import synth
+    skip = 8 * 3  # slice start: offsets base != 0, validity pointers 3 bytes into their allocation
+    host = synth.taxi_table(n + skip, backend="numpy")
+    dev_full = host.to("cuda")
+    cols = {}
+    for k, c in dev_full.items():
+        valid = None if c.valid is None else c.valid[skip // 8:]
+        if c.kind == "numeric":
+            v = c.values[skip:]
+            if v.data_ptr() % 16:  # kernels take 16-byte aligned value arrays: re-home the slice
+                v = v.clone()
+            cols[k] = ktw.NumericColumn(v, valid)
+        else:
+            off = c.offsets[skip:]
+            if off.data_ptr() % 16:
+                off = off.clone()
+            cols[k] = ktw.StringColumn(off, c.pool, valid, c.pool_bytes)
+    dev = ktw.Table(cols)
+    eng = ktw.Engine(ktw.trace(fn, synth.TAXI_SCHEMA))
+    got = eng.transform_state_free(dev)
+    torch.cuda.synchronize()
+    host_cols = helpers.oracle_from_table(host)
+    sl = {k: (O.StrCol(c.offsets[skip:] - c.offsets[skip], c.pool[c.offsets[skip]:], c.valid[skip:]) if isinstance(c, O.StrCol)
+              else O.NumCol(c.values[skip:], c.valid[skip:])) for k, c in host_cols.items()}
+    want = {k: O.fill_in_missing(sl[k[:-3]]) for k in got if k != "tips_xf"}
+    want["tips_xf"] = O.tips_label(O.fill_in_missing(sl["fare"]), O.fill_in_missing(sl["tips"]), 0.2)
+    assert set(got) == {"trip_start_hour_xf", "trip_start_day_xf", "trip_start_month_xf", "pickup_census_tract_xf", "dropoff_census_tract_xf",
+                        "pickup_community_area_xf", "dropoff_community_area_xf", "tips_xf"}
+    for k, col in got.items():
+        if col.kind == "string":
+            assert col.to_list() == list(want[k]), k
+        else:
+            assert np.array_equal(col.values.cpu().numpy(), want[k]), k
+
+
 def test_synthetic_generators_agree_on_gpu(ktw):
     """torch-on-GPU generator == numpy twin, bit for bit (the benchmark relies on it)."""
     from kubeflow_tfx_workshop_b200 import synth
