@@ -243,6 +243,12 @@ def _peak():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def _rows_per_rank(args, ktw, world):
+    if args.global_rows:
+        return [hi - lo for lo, hi in (ktw.shard_range(args.global_rows, r, world) for r in range(world))]
+    return [args.rows_per_gpu] * world
+
+
 def _workload(args, ktw, synth, dev, rank, world):
     """-> (plan, chunks, rows_local, description).  Shards are lists of chunks of <= chunk_rows rows."""
     import torch
@@ -299,11 +305,13 @@ def run_b200(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    rows_per_rank = _rows_per_rank(args, ktw, world)  # the benchmark sharded the rows itself: no gather of row counts
+
     def step(out):
         if args.no_overlap:
-            state = eng.analyze(chunks)
+            state = eng.analyze(chunks, rows_per_rank)
             return [eng.transform(c, state, o) for c, o in zip(chunks, out)], state
-        return eng.analyze_and_transform(chunks, out)
+        return eng.analyze_and_transform(chunks, out, rows_per_rank)
 
     # warm-up (also allocates every workspace and the output buffers)
     ring = args.out_ring if 0 < args.out_ring < len(chunks) else 0
@@ -338,7 +346,7 @@ def run_b200(args):
     a_ms = x_ms = 0.0
     for _ in range(reps):
         ev[0].record()
-        st2 = eng.analyze(chunks)
+        st2 = eng.analyze(chunks, rows_per_rank)
         ev[1].record()
         out = [eng.transform(c, st2, o) for c, o in zip(chunks, out)]
         ev[2].record()

@@ -189,11 +189,14 @@ TXF_API int txf_vocab_export_blob(const void* table_dev, const uint8_t* arena_de
 TXF_API int txf_vocab_insert_blob(const uint64_t* blob_dev, int64_t stride_words, int64_t section_offset_words, int nranks,
                           int64_t K, int64_t S, void* table_dev, int64_t capacity, uint8_t* arena_dev,
                           int64_t arena_cap, uint64_t* ctrl_dev, txf_stream_t stream);
-/* add m serialised entries (another rank's export) into a table */
+/* add m serialised entries (the ranks' exports) into a table.  owners > 1: only the entries whose key
+ * hashes to `owner` (mod owners) are added -- every rank sees all entries and re-counts its own share,
+ * which yields exact global counts per term at 1/owners of the insert work (the Beam CombinePerKey the
+ * reference relies on, SURVEY.md 3.1, partitions by key the same way); owners = 1 adds everything. */
 TXF_API int txf_vocab_insert(const uint64_t* fp_dev, const uint64_t* tag_dev, const uint64_t* count_dev,
-                     const int64_t* offsets_dev, const uint8_t* pool_dev, int64_t m, void* table_dev,
-                     int64_t capacity, uint8_t* arena_dev, int64_t arena_cap, uint64_t* ctrl_dev,
-                     txf_stream_t stream);
+                     const int64_t* offsets_dev, const uint8_t* pool_dev, int64_t m, int owners, int owner,
+                     void* table_dev, int64_t capacity, uint8_t* arena_dev, int64_t arena_cap,
+                     uint64_t* ctrl_dev, txf_stream_t stream);
 /* keep entries with count >= *threshold_key_dev: ent_out_dev, ctrl[5] = how many */
 TXF_API int txf_vocab_filter_ge(const uint32_t* ent_dev, const uint32_t* counts_dev, int64_t m,
                         const uint32_t* threshold_key_dev, uint32_t* ent_out_dev, uint64_t* ctrl_dev,

@@ -375,10 +375,12 @@ __global__ void __launch_bounds__(kVcWarps * 32, 1) __maxnreg__(kVcWarps == kVcW
 
 __global__ void vocab_insert_kernel(const uint64_t* __restrict__ fp, const uint64_t* __restrict__ tag,
                                     const uint64_t* __restrict__ count, const int64_t* __restrict__ offsets,
-                                    const uint8_t* __restrict__ pool, int64_t m, CountSlot* table, uint64_t mask,
-                                    uint8_t* arena, int64_t arena_cap, unsigned long long* ctrl) {
+                                    const uint8_t* __restrict__ pool, int64_t m, uint32_t owners, uint32_t owner,
+                                    CountSlot* table, uint64_t mask, uint8_t* arena, int64_t arena_cap, unsigned long long* ctrl) {
   int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
   if (i >= m) return;
+  // owner-partitioned merge: every rank sees all entries and re-counts the terms whose identity hashes to it
+  if (owners > 1 && static_cast<uint32_t>(home_slot(fp[i], tag[i], 0xFFFFFFFFULL) >> 7) % owners != owner) return;
   table_add(table, mask, fp[i], tag[i], count[i], pool + offsets[i], static_cast<uint32_t>(offsets[i + 1] - offsets[i]), arena,
             arena_cap, ctrl);
 }
@@ -738,16 +740,18 @@ int txf_vocab_insert_blob(const uint64_t* blob_dev, int64_t stride_words, int64_
 }
 
 int txf_vocab_insert(const uint64_t* fp_dev, const uint64_t* tag_dev, const uint64_t* count_dev, const int64_t* offsets_dev,
-                     const uint8_t* pool_dev, int64_t m, void* table_dev, int64_t capacity, uint8_t* arena_dev,
+                     const uint8_t* pool_dev, int64_t m, int owners, int owner, void* table_dev, int64_t capacity, uint8_t* arena_dev,
                      int64_t arena_cap, uint64_t* ctrl_dev, txf_stream_t stream) {
   using namespace txf;
   TXF_REQUIRE(m >= 0, "vocab_insert: negative m");
+  TXF_REQUIRE(owners >= 1 && owner >= 0 && owner < owners, "vocab_insert: owner %d out of [0,%d)", owner, owners);
   TXF_REQUIRE(pow2(capacity) && capacity < (1LL << 32), "vocab_insert: capacity must be a power of two below 2^32");
   if (m == 0) return TXF_OK;
   TXF_REQUIRE(fp_dev && tag_dev && count_dev && offsets_dev && pool_dev && table_dev && arena_dev && ctrl_dev, "vocab_insert: null pointer");
   vocab_insert_kernel<<<blocks_for(m, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      fp_dev, tag_dev, count_dev, offsets_dev, pool_dev, m, static_cast<CountSlot*>(table_dev),
-      static_cast<uint64_t>(capacity - 1), arena_dev, arena_cap, reinterpret_cast<unsigned long long*>(ctrl_dev));
+      fp_dev, tag_dev, count_dev, offsets_dev, pool_dev, m, static_cast<uint32_t>(owners), static_cast<uint32_t>(owner),
+      static_cast<CountSlot*>(table_dev), static_cast<uint64_t>(capacity - 1), arena_dev, arena_cap,
+      reinterpret_cast<unsigned long long*>(ctrl_dev));
   TXF_LAUNCH_CHECK();
   count_launch(1);
   return TXF_OK;

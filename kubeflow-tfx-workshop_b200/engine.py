@@ -207,6 +207,8 @@ class Engine:
         # anything that does not fit (more terms / longer terms / more candidates) falls back to the sized exchange
         self.fixed_exchange = True
         self.xchg_terms, self.xchg_term_bytes = 4096, 64
+        self.partition_vocab = True   # sized exchange: owners re-count their share of the terms (top_k vocabularies)
+        self.last_vocab_exchange: Dict[str, str] = {}
         self.timeline: Dict[str, float] = {}   # TXF_PROFILE=1: wall ms per analyze() segment (with device syncs)
         self._profile = os.environ.get("TXF_PROFILE") == "1"
         self.last_quantile_path: Dict[int, str] = {}
@@ -292,15 +294,22 @@ class Engine:
                 nat.i32_array([_DT[c.dtype] for c in cols]))
 
     # ---- analyze ------------------------------------------------------------------------------
-    def analyze(self, data: Union[Table, Sequence[Table]]) -> TransformState:
+    def analyze(self, data: Union[Table, Sequence[Table]], rows_per_rank: Optional[Sequence[int]] = None,
+                _side_work=None) -> TransformState:
         """One analyze pass.  The vocabulary count table and its byte arena start small; a pass that
-        fills either grows it and runs again (tft has no such knob), on every rank alike."""
+        fills either grows it and runs again (tft has no such knob), on every rank alike.
+        `rows_per_rank`: the number of rows every rank holds, when the caller knows it (it sharded the rows,
+        e.g. with `shard_range`); otherwise the counts are gathered, which costs a host round trip up front."""
         chunks = [data] if isinstance(data, Table) else list(data)
         for c in chunks:
             self._check_table(c)
+        if rows_per_rank is not None:
+            rows_per_rank = [int(v) for v in rows_per_rank]
+            if len(rows_per_rank) != self.comm.world or rows_per_rank[self.comm.rank] != sum(len(c) for c in chunks):
+                raise ValueError("rows_per_rank must list every rank's row count, this rank's included")
         while True:
             try:
-                return self._analyze_once(chunks)
+                return self._analyze_once(chunks, rows_per_rank, _side_work)
             except _VocabGrow as g:
                 if g.what == "table":
                     if self.vocab_capacity >= self.max_vocab_capacity:
@@ -314,8 +323,14 @@ class Engine:
                 for k in [k for k in self._ws if k[0].startswith("v_")]:
                     del self._ws[k]  # table / arena / code buffers are sized by the old capacity
 
-    def _analyze_once(self, chunks: List[Table]) -> TransformState:
+    def _analyze_once(self, chunks: List[Table], rows_per_rank: Optional[List[int]] = None, side_work=None) -> TransformState:
+        """side_work(events): analyze_and_transform's launch of the state-free stream kernel.  Single rank: first thing.
+        Multi-rank: only after the all-gather of the quantile samples (`events`) -- while that kernel sits on every SM a
+        collective kernel does not become resident (its shared-memory split differs and an SM only changes split when idle)."""
         n_local = sum(len(c) for c in chunks)
+        if side_work is not None and not self.comm.active:
+            side_work([])
+            side_work = None
         if self._profile:
             torch.cuda.synchronize(self.device)
             self._t0 = time.perf_counter()
@@ -323,7 +338,8 @@ class Engine:
         self._formatted.clear()
         # the three analyzer families are independent: queue them on three streams so that the
         # HBM-bound moments pass and the issue-bound counting passes share the SMs
-        pending_v = None
+        pending_v = pending_q = None
+        count_vocab = lambda: {vk: self._vocab_count(vk, spec, chunks) for vk, spec in self.vocab_specs.items()}
         if self.overlap_streams:
             if self._side is None:
                 self._side = (torch.cuda.Stream(device=self.device), torch.cuda.Stream(device=self.device))
@@ -332,11 +348,14 @@ class Engine:
             start.record(main)
             sv.wait_event(start)
             sq.wait_event(start)
-            # the vocabulary counts need nothing from the other ranks: they are queued before the
-            # row counts are gathered, so the GPU is already busy while the host waits for those
-            with torch.cuda.stream(sv):
-                pending_v = {vk: self._vocab_count(vk, spec, chunks) for vk, spec in self.vocab_specs.items()}
-        if self.comm.active:
+            if not self.comm.active or rows_per_rank is None:
+                # the vocabulary counts need nothing from the other ranks: they are queued before the
+                # row counts are gathered, so the GPU is already busy while the host waits for those
+                with torch.cuda.stream(sv):
+                    pending_v = count_vocab()
+        if rows_per_rank is not None:
+            n_locals = rows_per_rank
+        elif self.comm.active:
             nl = torch.tensor([n_local], dtype=torch.int64, device=self.device)
             n_locals = [int(v) for v in self.comm.all_gather(nl).flatten().tolist()]
         else:
@@ -344,22 +363,41 @@ class Engine:
         n_total = sum(n_locals)
         self._tick("row_counts")
         state = TransformState(plan=self.plan, moment_keys=list(self.moment_keys), mean_var=None, moments=None, num_rows=n_total)
+        # multi-rank: the Welford triples and min/max pairs travel inside the one fixed-layout exchange after the local pass
+        defer = self.comm.active and self.fixed_exchange and not self._profile
         if self.overlap_streams:
             with torch.cuda.stream(sq):
-                pending_q = {nb: self._quantiles_launch(nb, keys, chunks, n_locals) for nb, keys in self.bucket_groups.items()}
-            self._analyze_moments(chunks, state)
-            self._analyze_minmax(chunks, state)
+                pending_q = {nb: self._quantiles_sample(nb, keys, chunks, n_locals) for nb, keys in self.bucket_groups.items()}
+            if side_work is not None:
+                side_work([pq["gathered"] for pq in pending_q.values() if pq.get("gathered") is not None])
+                side_work = None
+            if pending_v is None:
+                # Row counts came from the caller, so nothing made the host wait above.  The count pass is queued right BEHIND
+                # the all-gather of the quantile samples (and before the rest of the quantile pipeline, which takes the host a
+                # millisecond to enqueue): a collective kernel cannot become resident once the persistent count CTAs (plus the
+                # stream kernel) hold every SM's registers, and the quantile pass would wait for the whole count pass.
+                for pq in pending_q.values():
+                    if pq.get("gathered") is not None:
+                        sv.wait_event(pq["gathered"])
+                with torch.cuda.stream(sv):
+                    pending_v = count_vocab()
+            with torch.cuda.stream(sq):
+                pending_q = {nb: self._quantiles_count(nb, pq, chunks) for nb, pq in pending_q.items()}
+            self._analyze_moments(chunks, state, defer)
+            self._analyze_minmax(chunks, state, defer)
             main.wait_stream(sv)
             main.wait_stream(sq)
         else:
-            self._analyze_moments(chunks, state)
-            self._analyze_minmax(chunks, state)
+            if side_work is not None:
+                side_work([])
+            self._analyze_moments(chunks, state, defer)
+            self._analyze_minmax(chunks, state, defer)
             pending_q = {nb: self._quantiles_launch(nb, keys, chunks, n_locals) for nb, keys in self.bucket_groups.items()}
-            pending_v = {vk: self._vocab_count(vk, spec, chunks) for vk, spec in self.vocab_specs.items()}
+            pending_v = count_vocab()
         if self.comm.active and self.fixed_exchange and not self._profile:
             # the fixed-layout exchange needs no value from the host: queue it behind the local pass
             # so that its launches are issued while the GPU is still busy, then wait once
-            self._exchange_fixed(pending_q, pending_v)
+            self._exchange_fixed(pending_q, pending_v, state)
             main.synchronize()
         else:
             # one host round trip: everything queued above has to finish before sizes/flags are read
@@ -367,7 +405,7 @@ class Engine:
             self._tick("local_pass")
             if self.comm.active:
                 if self.fixed_exchange:
-                    self._exchange_fixed(pending_q, pending_v)
+                    self._exchange_fixed(pending_q, pending_v, None)
                 else:
                     self._exchange(pending_q, pending_v)
                 self._tick("exchange")
@@ -384,7 +422,7 @@ class Engine:
         return state
 
     # -- moments
-    def _analyze_moments(self, chunks, state: TransformState):
+    def _analyze_moments(self, chunks, state: TransformState, defer_merge: bool = False):
         nm = len(self.moment_keys)
         if nm == 0:
             return
@@ -396,15 +434,25 @@ class Engine:
                 continue
             v, m, d = self._num_args([ch[k] for k in self.moment_keys])
             nat.call("txf_moments_update", v, m, d, nm, len(ch), mstate.data_ptr(), ws.data_ptr(), s)
-        if self.comm.active:
-            gathered = self.comm.all_gather(mstate)  # [W, nm, 3], rank order
+        state.moments = mstate
+        if defer_merge:
+            return
+        gathered = self.comm.all_gather(mstate) if self.comm.active else None  # [W, nm, 3], rank order
+        self._finish_moments(state, gathered)
+
+    def _finish_moments(self, state: TransformState, gathered: Optional[torch.Tensor]):
+        """Chan merge of the ranks' triples in rank order (bit-identical on every rank), then (mean, variance) as fp32."""
+        nm = len(self.moment_keys)
+        s = self._stream()
+        mstate = state.moments
+        if gathered is not None:
             nat.call("txf_moments_merge", gathered.data_ptr(), self.comm.world, nm, mstate.data_ptr(), s)
         mv = self._buf("mean_var", (nm, 2), torch.float32)
         nat.call("txf_moments_finalize", mstate.data_ptr(), nm, mv.data_ptr(), s)
-        state.moments, state.mean_var = mstate, mv
+        state.mean_var = mv
 
     # -- min/max (tft.scale_to_0_1 / scale_by_min_max, tft.min / tft.max)
-    def _analyze_minmax(self, chunks, state: TransformState):
+    def _analyze_minmax(self, chunks, state: TransformState, defer_merge: bool = False):
         nm = len(self.minmax_keys)
         if nm == 0:
             return
@@ -417,11 +465,15 @@ class Engine:
                 continue
             v, m, d = self._num_args([ch[k] for k in self.minmax_keys])
             nat.call("txf_minmax_update", v, m, d, nm, len(ch), mm.data_ptr(), ws.data_ptr(), s)
-        if self.comm.active:
-            gathered = self.comm.all_gather(mm)  # [W, nm, 2]
-            nat.call("txf_minmax_begin", mm.data_ptr(), nm, s)
-            nat.call("txf_minmax_merge", gathered.data_ptr(), self.comm.world, nm, mm.data_ptr(), s)
         state.minmax_keys, state.minmax = list(self.minmax_keys), mm
+        if self.comm.active and not defer_merge:
+            self._finish_minmax(state, self.comm.all_gather(mm))  # [W, nm, 2]
+
+    def _finish_minmax(self, state: TransformState, gathered: torch.Tensor):
+        nm = len(self.minmax_keys)
+        s = self._stream()
+        nat.call("txf_minmax_begin", state.minmax.data_ptr(), nm, s)
+        nat.call("txf_minmax_merge", gathered.data_ptr(), self.comm.world, nm, state.minmax.data_ptr(), s)
 
     # -- tf.as_string(int64 feature): the decimal text of every cell as a string column
     def _vocab_source(self, table: Table, spec) -> StringColumn:
@@ -474,6 +526,11 @@ class Engine:
     # -- quantiles
     def _quantiles_launch(self, nb: int, keys: List[str], chunks, n_locals: List[int]):
         """Queue the sample-select pipeline for one num_buckets group; returns what _finish needs."""
+        return self._quantiles_count(nb, self._quantiles_sample(nb, keys, chunks, n_locals), chunks)
+
+    def _quantiles_sample(self, nb: int, keys: List[str], chunks, n_locals: List[int]):
+        """First half of the pipeline: the stratified sample of this rank's rows and, multi-rank, its
+        all-gather (pend["gathered"]: event after that collective)."""
         T = nb - 1
         n_total = sum(n_locals)
         n_local = n_locals[self.comm.rank]
@@ -521,12 +578,24 @@ class Engine:
             pad = self._buf(f"q{nb}_sample_pad", (ncols, Mmax), torch.int32, zero=True)
             pad[:, :M_have] = sample
             g = self.comm.all_gather(pad)  # [W, ncols, Mmax]
+            pend["gathered"] = torch.cuda.Event()
+            pend["gathered"].record(torch.cuda.current_stream())
             # ranks whose chunks could not supply their share contribute what they have; the
             # order statistics below are taken over the slots every rank agreed on (host arithmetic)
             sample = torch.cat([g[r, :, : M_ranks[r]] for r in range(self.comm.world)], dim=1).contiguous()
             if M_have != M_local:
                 raise RuntimeError("sample size mismatch between chunks and plan")
-        sample = sample.contiguous()
+        pend["_ctx"] = (sample.contiguous(), edges_ranks, ranks, n_local)
+        return pend
+
+    def _quantiles_count(self, nb: int, pend, chunks):
+        """Second half: bracket edges from the sample, then the one counting pass over the columns."""
+        if "_ctx" not in pend:
+            return pend
+        sample, edges_ranks, ranks, n_local = pend.pop("_ctx")
+        keys, T = pend["keys"], pend["T"]
+        ncols = len(keys)
+        s = self._stream()
         M_sum = sample.shape[1]
         # (2) bracket edges = exact order statistics of the sample
         er = self._host_const([edges_ranks] * ncols, torch.int64)
@@ -591,7 +660,7 @@ class Engine:
         over = (counts_all > caps_all).any(dim=0)
         return torch.where(over, torch.full_like(counts_all[0], _NO_CAP + 1), counts_all.sum(dim=0)).contiguous()
 
-    def _exchange_fixed(self, pending_q, pending_v):
+    def _exchange_fixed(self, pending_q, pending_v, state: Optional[TransformState]):
         """The exchange step as one collective: every rank packs its vocabulary entries, candidate
         keys and cell counts into a fixed-layout int64 buffer on the device, the buffers are
         all-gathered, and each rank rebuilds the merged state from all rows -- no size ever goes
@@ -609,9 +678,21 @@ class Engine:
             ncols, ncell = len(p["keys"]), 4 * p["T"] + 1
             layout[("q", nb)] = (off, off + ncols, off + ncols + 1)  # candidate counts, buffer capacity, cells
             off += ncols + 1 + ncols * ncell
+        nmom = len(self.moment_keys) if state is not None and state.moments is not None else 0
+        nmm = len(self.minmax_keys) if state is not None and state.minmax is not None else 0
+        if nmom:
+            layout["mom"] = off
+            off += 3 * nmom           # fp64 triples as their bit patterns
+        if nmm:
+            layout["mm"] = off
+            off += nmm                # (min, max) fp32 pairs as their bit patterns
         if off == 0:
             return
         blob = self._buf("xchg_blob", off, torch.int64)
+        if nmom:
+            blob[layout["mom"]: layout["mom"] + 3 * nmom].copy_(state.moments.view(torch.int64).flatten())
+        if nmm:
+            blob[layout["mm"]: layout["mm"] + nmm].copy_(state.minmax.view(torch.int64).flatten())
         for vk, p in voc:
             o = layout[("v", vk)]
             nat.call("txf_vocab_export_blob", p["table"].data_ptr(), p["arena"].data_ptr(), p["ent"].data_ptr(), p["ctrl"].data_ptr(),
@@ -623,6 +704,12 @@ class Engine:
             blob[ok:ox].fill_(p["cand_cap"])
             blob[ox:ox + p["cells"].numel()].copy_(p["cells"].flatten())
         g = self.comm.all_gather(blob)  # [W, off] -- the one collective of the exchange
+        if nmom:
+            o = layout["mom"]
+            self._finish_moments(state, g[:, o:o + 3 * nmom].contiguous().view(torch.float64))
+        if nmm:
+            o = layout["mm"]
+            self._finish_minmax(state, g[:, o:o + nmm].contiguous().view(torch.float32))
         for nb, p in fast:
             ncols = len(p["keys"])
             oc, ok, ox = layout[("q", nb)]
@@ -697,14 +784,56 @@ class Engine:
             g_off = torch.zeros(m + 1, dtype=torch.int64, device=dev)
             if m:
                 torch.cumsum(g_len, 0, out=g_off[1:])
+            spec = self.vocab_specs[vk]
+            if self.partition_vocab and spec.top_k is not None and not spec.frequency_threshold and W > 1:
+                if self._exchange_owned(vk, spec, p, (g_fp, g_tg, g_cnt, g_off, g_pool, m)):
+                    continue
             cap2 = max(self.vocab_capacity, _pow2_at_least(2 * max(m, 1)))
             tag2 = p["tag"] + "_merged"
             table, arena, ctrl, ent, counts_buf = self._vocab_bufs(tag2, cap2)
             nat.call("txf_vocab_insert", g_fp.data_ptr(), g_tg.data_ptr(), g_cnt.data_ptr(), g_off.data_ptr(), g_pool.data_ptr(), m,
-                     table.data_ptr(), cap2, arena.data_ptr(), self.arena_bytes, ctrl.data_ptr(), s)
+                     1, 0, table.data_ptr(), cap2, arena.data_ptr(), self.arena_bytes, ctrl.data_ptr(), s)
             nat.call("txf_vocab_compact", table.data_ptr(), cap2, arena.data_ptr(), ent.data_ptr(), counts_buf.data_ptr(),
                      ctrl.data_ptr(), s)
             p["merged"] = dict(tag=tag2, cap=cap2, table=table, arena=arena, ctrl=ctrl, ent=ent, counts=counts_buf)
+
+    def _exchange_owned(self, vk, spec: VocabSpec, p, gathered) -> bool:
+        """Owner-partitioned merge of a large vocabulary: of the entries of all ranks each
+        rank re-counts only the terms it OWNS (identity hash mod world), which gives exact global counts at
+        1/world of the insert work; the owners' top_k lists (a superset of the global top_k) are then
+        all-gathered in the fixed layout and merged everywhere.  Returns False (nothing changed) when an
+        owner's list does not fit the fixed layout (a term longer than the byte slot): the caller then
+        re-counts everything everywhere."""
+        dev, W, s = self.device, self.comm.world, self._stream()
+        g_fp, g_tg, g_cnt, g_off, g_pool, m = gathered
+        capo = max(self.vocab_capacity, _pow2_at_least(2 * (m // W + 1024)))
+        tago = p["tag"] + "_owned"
+        table, arena, ctrl, ent, counts_buf = self._vocab_bufs(tago, capo)
+        nat.call("txf_vocab_insert", g_fp.data_ptr(), g_tg.data_ptr(), g_cnt.data_ptr(), g_off.data_ptr(), g_pool.data_ptr(), m,
+                 W, self.comm.rank, table.data_ptr(), capo, arena.data_ptr(), self.arena_bytes, ctrl.data_ptr(), s)
+        nat.call("txf_vocab_compact", table.data_ptr(), capo, arena.data_ptr(), ent.data_ptr(), counts_buf.data_ptr(), ctrl.data_ptr(), s)
+        owned = dict(tag=tago, cap=capo, table=table, arena=arena, ctrl=ctrl, ent=ent, counts=counts_buf)
+        ctrl_host = ctrl.cpu().tolist()
+        sel, k = self._select_top(owned, spec, int(ctrl_host[3]))
+        # the owner's list in the fixed layout: K = top_k slots; the header carries this rank's flags and k
+        K, S = int(spec.top_k), self.xchg_term_bytes
+        words = 1 + 4 * K + K * S // 8
+        sec = self._buf(f"{tago}_sec", words, torch.int64)
+        hdr = ctrl.clone()
+        hdr[3] = k
+        nat.call("txf_vocab_export_blob", table.data_ptr(), arena.data_ptr(), sel.data_ptr(), hdr.data_ptr(), K, S, sec.data_ptr(), s)
+        g = self.comm.all_gather(sec)  # [W, words]
+        capf = max(1 << 12, _pow2_at_least(2 * W * K))
+        tagf = p["tag"] + "_merged"
+        tablef, arenaf, ctrlf, entf, countsf = self._vocab_bufs(tagf, capf)
+        nat.call("txf_vocab_insert_blob", g.data_ptr(), words, 0, W, K, S, tablef.data_ptr(), capf, arenaf.data_ptr(), self.arena_bytes,
+                 ctrlf.data_ptr(), s)
+        nat.call("txf_vocab_compact", tablef.data_ptr(), capf, arenaf.data_ptr(), entf.data_ptr(), countsf.data_ptr(), ctrlf.data_ptr(), s)
+        if int(ctrlf[2].item()) & 4:  # a term longer than the byte slot (the same verdict on every rank)
+            return False
+        p["merged"] = dict(tag=tagf, cap=capf, table=tablef, arena=arenaf, ctrl=ctrlf, ent=entf, counts=countsf)
+        self.last_vocab_exchange[vk[0]] = "owner-partitioned"
+        return True
 
     def _quantiles_general(self, nb: int, keys: List[str], chunks, n_total: int) -> BucketResult:
         """Exact radix select over the whole column (any number of boundaries)."""
@@ -814,23 +943,10 @@ class Engine:
             state.codes[(vk, i)] = CodedChunk(weakref.ref(ch), col.offsets.data_ptr(), col.pool.data_ptr(), _ptr(col.valid), len(ch),
                                               codes, final)
 
-    def _vocab_finish(self, vk: Tuple, spec: VocabSpec, pend) -> VocabResult:
+    def _select_top(self, pend, spec: VocabSpec, kept: int):
+        """The first min(top_k, kept) entries of a compacted count table by (count, bytes) descending
+        (after the frequency threshold): -> (entry list on the device, sorted; k)."""
         s = self._stream()
-        ctrl_host = pend["ctrl"].cpu().tolist()
-        kept = int(ctrl_host[3])
-        if not self.comm.active:
-            self._check_vocab_flags(int(ctrl_host[2]), int(ctrl_host[1]), spec)
-        else:
-            # every decision below is taken on values that are identical on all ranks: the merged table's
-            # flags, which carry the OR of every rank's local flags (bit 6, detail in bits 8..13)
-            m = int(pend["merged"]["ctrl"][2].item())
-            self._check_vocab_flags((((m >> 8) & 0x3F) | pend.get("peer_flags", 0)) & ~4, None, spec)  # some rank's local pass
-            if m & 4:  # a fixed-layout section overflowed on some rank: sized exchange
-                self._exchange({}, {vk: pend})
-            ctrl_m = pend["merged"]["ctrl"].cpu().tolist()
-            self._check_vocab_flags(int(ctrl_m[2]) & 0x3F & ~4, None, spec)                            # the merged table
-            pend = pend["merged"]  # every rank's admitted entries, re-counted into one table
-            kept = int(ctrl_m[3])
         tag, table, arena, ctrl, ent, counts = (pend[k] for k in ("tag", "table", "arena", "ctrl", "ent", "counts"))
         k = kept if spec.top_k is None else min(spec.top_k, kept)
         if spec.frequency_threshold and kept:
@@ -856,6 +972,29 @@ class Engine:
             m = int(ctrl[5].item())
         scratch = self._buf(f"{tag}_sort", max(nat.query("txf_vocab_sort_scratch_bytes", m), 16), torch.uint8)
         nat.call("txf_vocab_sort", table.data_ptr(), arena.data_ptr(), sel.data_ptr(), m, scratch.data_ptr(), s)
+        return sel, k
+
+    def _vocab_finish(self, vk: Tuple, spec: VocabSpec, pend) -> VocabResult:
+        s = self._stream()
+        ctrl_host = pend["ctrl"].cpu().tolist()
+        kept = int(ctrl_host[3])
+        if not self.comm.active:
+            self._check_vocab_flags(int(ctrl_host[2]), int(ctrl_host[1]), spec)
+        else:
+            # every decision below is taken on values that are identical on all ranks: the merged table's
+            # flags, which carry the OR of every rank's local flags (bit 6, detail in bits 8..13)
+            m = int(pend["merged"]["ctrl"][2].item())
+            self._check_vocab_flags((((m >> 8) & 0x3F) | pend.get("peer_flags", 0)) & ~4, None, spec)  # some rank's local pass
+            if m & 4:  # a fixed-layout section overflowed on some rank: sized exchange
+                self._exchange({}, {vk: pend})
+                m = int(pend["merged"]["ctrl"][2].item())  # owner tables of the partitioned merge report their flags the same way
+                self._check_vocab_flags((((m >> 8) & 0x3F) | pend.get("peer_flags", 0)) & ~4, None, spec)
+            ctrl_m = pend["merged"]["ctrl"].cpu().tolist()
+            self._check_vocab_flags(int(ctrl_m[2]) & 0x3F & ~4, None, spec)                            # the merged table
+            pend = pend["merged"]  # every rank's admitted entries, re-counted into one table
+            kept = int(ctrl_m[3])
+        tag, table, arena = pend["tag"], pend["table"], pend["arena"]
+        sel, k = self._select_top(pend, spec, kept)
         lookup_cap = _pow2_at_least(max(2 * (spec.top_k if spec.top_k is not None else k), 2 * k, 2))
         lookup = self._buf(f"{tag}_lookup", nat.query("txf_vocab_lookup_bytes", lookup_cap), torch.uint8)
         if k == 0:
@@ -1049,13 +1188,13 @@ class Engine:
         order = [sp.out_key for sp in self.plan.specs if sp.out_key in cols and not sp.out_key.startswith(TEMP_PREFIX)]
         return Table({k: cols[k] for k in order})
 
-    def analyze_and_transform(self, data: Union[Table, Sequence[Table]], out=None):
+    def analyze_and_transform(self, data: Union[Table, Sequence[Table]], out=None, rows_per_rank: Optional[Sequence[int]] = None):
         """The single pass tft_beam.AnalyzeAndTransformDataset makes (notebooks/06_...:236-262): analyze the
         rows and transform the same rows.  The ops that need no analyzer result (pass-throughs, label: half
         of the transform's bytes) are queued first, on a second stream, as the small-footprint streaming
         kernel; the analyzers -- issue- and latency-bound, a quarter of the HBM bandwidth -- run next to it
         (the count pass in its 24-warp shape), and the ops that need their results follow.  `out`: output
-        table(s) of an earlier call whose buffers are reused."""
+        table(s) of an earlier call whose buffers are reused; `rows_per_rank`: see `analyze`."""
         chunks = [data] if isinstance(data, Table) else list(data)
         outs_prev = [out] if isinstance(out, Table) else (list(out) if out is not None else [None] * len(chunks))
         free = [sp for sp in self.plan.specs if self._state_free(sp)]
@@ -1069,15 +1208,20 @@ class Engine:
                 self._xstream = torch.cuda.Stream(device=self.device)
             xs = self._xstream
             xs.wait_stream(main)
-            with torch.cuda.stream(xs):
-                done = [self.transform_state_free(c, o) for c, o in zip(chunks, outs_prev)]
-            for d in done:  # buffers allocated under the side stream are handed to the caller's stream
-                for col in d.values():
-                    for t in ((col.values,) if isinstance(col, NumericColumn) else (col.offsets, col.pool)):
-                        t.record_stream(main)
+
+            def side_work(events):  # called by analyze at the point where the stream kernel may start (see _analyze_once)
+                for ev in events:
+                    xs.wait_event(ev)
+                with torch.cuda.stream(xs):
+                    done[:] = [self.transform_state_free(c, o) for c, o in zip(chunks, outs_prev)]
+                for d in done:  # buffers allocated under the side stream are handed to the caller's stream
+                    for col in d.values():
+                        for t in ((col.values,) if isinstance(col, NumericColumn) else (col.offsets, col.pool)):
+                            t.record_stream(main)
+
             self._count_warps = 24
         try:
-            state = self.analyze(chunks)
+            state = self.analyze(chunks, rows_per_rank, side_work if overlap else None)
         finally:
             self._count_warps = 0
         outs = [self.transform(c, state, o, d) for c, o, d in zip(chunks, outs_prev, done)]

@@ -352,3 +352,66 @@ def concat_tables(parts: List[Table]) -> Table:
         else:
             out[name] = NumericColumn(torch.cat([c.values for c in cols]), valid)
     return Table(out)
+
+
+# ------------------------------------------------------------------------------------------------
+# stress workloads (BASELINE.json configs[3] and configs[4]); torch only, generated on the device
+# ------------------------------------------------------------------------------------------------
+def decimal_string_column(ids: torch.Tensor) -> StringColumn:
+    """The decimal text of every int64 as a string column (what tf.as_string gives), built with the
+    library's own formatting kernels.  Data plumbing for the stress workloads, outside any timed region."""
+    from . import _native as nat
+    n = ids.numel()
+    dev = ids.device
+    with torch.cuda.device(dev):
+        s = torch.cuda.current_stream().cuda_stream
+        lens = torch.empty(n, dtype=torch.int32, device=dev)
+        nat.call("txf_i64_format_lengths", ids.data_ptr(), None, n, lens.data_ptr(), s)
+        ends = torch.cumsum(lens, 0, dtype=torch.int64)
+        total = int(ends[-1].item())
+        if total >= 1 << 31:
+            raise ValueError("string pool exceeds 2^31-1 bytes; generate fewer rows per chunk")
+        offsets = torch.zeros(n + 1, dtype=torch.int32, device=dev)
+        offsets[1:] = ends.to(torch.int32)
+        pool = torch.zeros(total + POOL_SLACK, dtype=torch.uint8, device=dev)
+        nat.call("txf_i64_format_write", ids.data_ptr(), None, n, offsets.data_ptr(), pool.data_ptr(), s)
+    return StringColumn(offsets, pool, None, total)
+
+
+def vocab_stress_table(n: int, row0: int = 0, n_distinct: int = 10_000_000, seed: int = SEED, device="cuda") -> Table:
+    """Two string columns over `n_distinct` distinct terms each with a skewed popularity (term index =
+    floor(D u^3)): `code` holds terms of at most 13 bytes (their own key), `name` terms of 18-20 bytes
+    (fingerprint class).  Rows are a pure function of (seed, row), so ranks generate disjoint shards."""
+    xp = _Th(device)
+    rows = xp.rows(row0, row0 + n)
+    cols = {}
+    for name, stream, shift in (("code", 2001, 24), ("name", 2002, 1)):
+        u = _mix(xp, rows, seed, stream)
+        a = ((u >> 11) & ((1 << 53) - 1)).to(torch.float64) * (1.0 / (1 << 53))
+        idx = (a * a * a * n_distinct).to(torch.int64).clamp_(max=n_distinct - 1)
+        ids = _mix(xp, idx, seed, stream + 10)  # scrambled 64-bit id of the term
+        ids = (ids >> shift) & ((1 << (63 - shift)) - 1) if shift > 1 else ids & ((1 << 62) - 1) | (1 << 61)
+        cols[name] = decimal_string_column(ids.contiguous())
+    return Table(cols)
+
+
+def bucket_stress_table(n: int, row0: int = 0, seed: int = SEED, device="cuda") -> Table:
+    """Eight float32 lat/long-style columns: four drawn from ~800 centroids with a skewed popularity and
+    3.2 % missing cells (heavy duplicates, an atom at 0.0 after fill-missing), four fine-grained."""
+    xp = _Th(device)
+    rows = xp.rows(row0, row0 + n)
+    lat_np, lon_np = centroid_tables(seed)
+    cent = [xp.table(lat_np), xp.table(lon_np)]
+    cols = {}
+    for c in range(8):
+        if c < 4:
+            idx = _skewed_index(xp, rows, seed, "pickup_latitude", 4 * c + 3, N_CENTROIDS)
+            x = (xp.take(cent[c & 1], idx) + float(c)).to(torch.float32)
+            present = _draw(xp, rows, seed, "dropoff_latitude", 8 + c) % 1000 >= 32
+            bits = torch.from_numpy(np.packbits(present.cpu().numpy(), bitorder="little")).to(device)
+            cols[f"c{c}"] = NumericColumn(x.contiguous(), bits)
+        else:
+            u = _draw(xp, rows, seed, "pickup_longitude", 8 + c)  # 31-bit draw
+            x = (u.to(torch.float32) * float(np.float32(2.0 ** -31)) * 0.5 - 87.9 + float(c)).to(torch.float32)
+            cols[f"c{c}"] = NumericColumn(x.contiguous(), None)
+    return Table(cols)

@@ -40,7 +40,9 @@ def main():
         eng.fixed_exchange = fixed
         if tiny:
             eng.xchg_terms = 8
-        out, state = eng.analyze_and_transform(shard_host.to(f"cuda:{local}"))
+        # the caller sharded the rows itself: every second configuration passes the row counts instead of having them gathered
+        rpr = [b - a for a, b in (ktw.shard_range(n, r, world) for r in range(world))] if fixed and not tiny else None
+        out, state = eng.analyze_and_transform(shard_host.to(f"cuda:{local}"), rows_per_rank=rpr)
         torch.cuda.synchronize()
         # identical state on every rank
         sig = []
@@ -104,6 +106,36 @@ def main():
     assert np.array_equal(out["area"].values.cpu().numpy(), O.apply_vocabulary(strings, vocab, num_oov_buckets=3)[lo:hi])
     if rank == 0:
         print(f"multi-gpu sibling parity ok: world={world} rows={n}", flush=True)
+    # configs[3] across ranks: millions of distinct terms per column -> the fixed-layout sections overflow, the sized
+    # exchange runs, and (top_k vocabulary) every rank re-counts only the terms it owns.  Checked against a single-rank
+    # engine that sees the rows of all ranks, and against the all-entries-everywhere merge.
+    class NoComm:
+        active, enabled, rank, world = False, False, 0, 1
+
+    spec = __import__("importlib.util").util.spec_from_file_location("stress", os.path.join(ROOT, "examples", "stress_preprocessing.py"))
+    with ktw.install_shims():
+        stress = __import__("importlib.util").util.module_from_spec(spec)
+        spec.loader.exec_module(stress)
+    nv, D = 3_000_000, 2_000_000
+    dev = f"cuda:{local}"
+    mine = synth.vocab_stress_table(nv, row0=rank * nv, n_distinct=D, device=dev)
+    plan = ktw.trace(stress.vocab_stress_fn, mine.schema())
+    solo = ktw.Engine(plan, device=dev, comm=NoComm(), vocab_capacity=1 << 23, arena_bytes=1 << 27)
+    everyone = [synth.vocab_stress_table(nv, row0=r * nv, n_distinct=D, device=dev) for r in range(world)]
+    st1 = solo.analyze(everyone)
+    want_ids = solo.transform(everyone[rank], st1)
+    for partition in (True, False):
+        eng = ktw.Engine(plan, device=dev, comm=comm, vocab_capacity=1 << 23, arena_bytes=1 << 27)
+        eng.partition_vocab = partition
+        out, state = eng.analyze_and_transform(mine, rows_per_rank=[nv] * world)
+        torch.cuda.synchronize()
+        assert set(eng.last_vocab_exchange.values()) == ({"owner-partitioned"} if partition else set()), eng.last_vocab_exchange
+        for key, res in state.vocabs.items():
+            assert res.terms() == st1.vocabs[key].terms(), (key, partition)
+        for k in out.keys():
+            assert torch.equal(out[k].values, want_ids[k].values), (k, partition)
+    if rank == 0:
+        print(f"multi-gpu vocabulary stress parity ok: world={world} rows/rank={nv} distinct={D}", flush=True)
     dist.barrier()
     dist.destroy_process_group()
 

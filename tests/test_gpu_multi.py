@@ -19,3 +19,4 @@ def test_two_rank_nccl_parity():
     assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
     assert out.stdout.count("multi-gpu parity ok") == 4
     assert out.stdout.count("multi-gpu sibling parity ok") == 1
+    assert out.stdout.count("multi-gpu vocabulary stress parity ok") == 1
