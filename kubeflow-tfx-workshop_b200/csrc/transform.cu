@@ -179,6 +179,7 @@ __device__ __forceinline__ float4 fill_f4(float4 r, uint32_t m) {
 }
 
 constexpr int kLinearBuckets = 32;  // up to 32 boundaries: count them for a whole quad, one broadcast LDS each
+constexpr int kSmemBuckets = 1024;  // up to 1024 boundaries (num_buckets <= 1000 and then some) are staged in shared memory per block
 struct NumParams {  // per-op constants of the numeric kinds
   ZScale z;
   const float* b;
@@ -286,7 +287,7 @@ __device__ __forceinline__ bool op_in8(const XfOp& op) {
 }
 
 __global__ void __launch_bounds__(kTileThreads) transform_tiles_kernel(const __grid_constant__ TileProgram tp, int64_t n) {
-  __shared__ float s_bounds[kLinearBuckets];
+  __shared__ float s_bounds[kSmemBuckets];
   const int nops = tp.prog.nops;
   int o = 0;
   while (o + 1 < nops && static_cast<int64_t>(blockIdx.x) >= tp.first_block[o + 1]) ++o;  // block-uniform, <= 32 steps
@@ -301,8 +302,8 @@ __global__ void __launch_bounds__(kTileThreads) transform_tiles_kernel(const __g
   if (kind == TXF_OP_BUCKETIZE) {
     p.nb = *static_cast<const int32_t*>(op.p1);
     p.b = static_cast<const float*>(op.p0);
-    if (p.nb <= kLinearBuckets) {  // the few boundaries of the linear count: one shared copy per block
-      if (static_cast<int>(threadIdx.x) < p.nb) s_bounds[threadIdx.x] = p.b[threadIdx.x];
+    if (p.nb <= kSmemBuckets) {  // one shared copy per block: the linear count (<= 32) and the binary search both read it there
+      for (int i = threadIdx.x; i < p.nb; i += kTileThreads) s_bounds[i] = p.b[i];
       __syncthreads();
       p.b = s_bounds;
     }

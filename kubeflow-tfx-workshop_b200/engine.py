@@ -295,7 +295,7 @@ class Engine:
 
     # ---- analyze ------------------------------------------------------------------------------
     def analyze(self, data: Union[Table, Sequence[Table]], rows_per_rank: Optional[Sequence[int]] = None,
-                _side_work=None) -> TransformState:
+                _side_work=None, _between=None) -> TransformState:
         """One analyze pass.  The vocabulary count table and its byte arena start small; a pass that
         fills either grows it and runs again (tft has no such knob), on every rank alike.
         `rows_per_rank`: the number of rows every rank holds, when the caller knows it (it sharded the rows,
@@ -309,7 +309,7 @@ class Engine:
                 raise ValueError("rows_per_rank must list every rank's row count, this rank's included")
         while True:
             try:
-                return self._analyze_once(chunks, rows_per_rank, _side_work)
+                return self._analyze_once(chunks, rows_per_rank, _side_work, _between)
             except _VocabGrow as g:
                 if g.what == "table":
                     if self.vocab_capacity >= self.max_vocab_capacity:
@@ -323,8 +323,12 @@ class Engine:
                 for k in [k for k in self._ws if k[0].startswith("v_")]:
                     del self._ws[k]  # table / arena / code buffers are sized by the old capacity
 
-    def _analyze_once(self, chunks: List[Table], rows_per_rank: Optional[List[int]] = None, side_work=None) -> TransformState:
-        """side_work(events): analyze_and_transform's launch of the state-free stream kernel.  Single rank: first thing.
+    def _analyze_once(self, chunks: List[Table], rows_per_rank: Optional[List[int]] = None, side_work=None,
+                      between=None) -> TransformState:
+        """between(state): called once moments and bucket boundaries are final and before the vocabularies are ranked;
+        analyze_and_transform queues the ops that need only those there, so that the launch-bound ranking chain
+        (compact, select, sort, lookup, decode tables -- a dozen tiny kernels and a few host reads) runs next to them.
+        side_work(events): analyze_and_transform's launch of the state-free stream kernel.  Single rank: first thing.
         Multi-rank: only after the all-gather of the quantile samples (`events`) -- while that kernel sits on every SM a
         collective kernel does not become resident (its shared-memory split differs and an SM only changes split when idle)."""
         n_local = sum(len(c) for c in chunks)
@@ -412,12 +416,19 @@ class Engine:
         for nb, pend in pending_q.items():
             state.buckets[nb] = self._quantiles_finish(nb, pend, chunks, n_total)
         self._tick("quantiles_finish")
-        for vk, pend in pending_v.items():
-            state.vocabs[vk] = self._vocab_finish(vk, self.vocab_specs[vk], pend)
-            for spec in self.plan.of(VocabSpec):  # decode tables depend on num_oov_buckets / default_value
-                if _vocab_key(spec) == vk:
-                    self._decode_tables(vk, spec, pend, state.vocabs[vk], state)
-                    break
+        rank_stream = main
+        if between is not None and self.overlap_streams and pending_v:
+            between(state)
+            rank_stream = self._side[1]  # everything queued so far has completed (host sync above): no event needed to start
+        with torch.cuda.stream(rank_stream):
+            for vk, pend in pending_v.items():
+                state.vocabs[vk] = self._vocab_finish(vk, self.vocab_specs[vk], pend)
+                for spec in self.plan.of(VocabSpec):  # decode tables depend on num_oov_buckets / default_value
+                    if _vocab_key(spec) == vk:
+                        self._decode_tables(vk, spec, pend, state.vocabs[vk], state)
+                        break
+        if rank_stream is not main:
+            main.wait_stream(rank_stream)
         self._tick("vocab_finish")
         return state
 
@@ -1220,8 +1231,14 @@ class Engine:
                             t.record_stream(main)
 
             self._count_warps = 24
+        def between(state):  # ops that need moments / boundaries only: queued while the vocabularies are still being ranked
+            for i, (c, o) in enumerate(zip(chunks, outs_prev)):
+                early = [sp for sp in self.plan.specs if isinstance(sp, (ZScoreSpec, BucketSpec))]
+                cols = self._run_fused(c, state, o, early, stream_kernel=False)
+                done[i] = dict(done[i] or {}, **cols)
+
         try:
-            state = self.analyze(chunks, rows_per_rank, side_work if overlap else None)
+            state = self.analyze(chunks, rows_per_rank, side_work if overlap else None, between if overlap else None)
         finally:
             self._count_warps = 0
         outs = [self.transform(c, state, o, d) for c, o, d in zip(chunks, outs_prev, done)]

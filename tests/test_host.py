@@ -214,6 +214,55 @@ int main(int argc, char** argv) {
     assert [int(k[2], 16) for k in keys] == O.key_to_f32(O.order_key(probes)).view(np.uint32).tolist()
 
 
+def test_fingerprint64_long_inputs_device_header_vs_c_oracle(tmp_path):
+    """Fingerprint64 for inputs longer than 32 bytes has no reference-held vector.  What this box
+    allows: the device header (csrc/farmhash.cuh, compiled for the host) against the separately written C oracle
+    on 10^5 random strings of 33-4096 bytes.  Two restatements of the same published algorithm agreeing is
+    consistency, not a pin."""
+    src = tmp_path / "fp.cu"
+    src.write_text(r'''
+#include <cstdio>
+#include <cstring>
+#include <vector>
+#include "common.cuh"
+#include "farmhash.cuh"
+namespace txf { void set_error(const char*, ...) {} int check_cuda(cudaError_t, const char*) { return 0; } void count_launch(int) {} }
+int main(int argc, char** argv) {
+  FILE* f = fopen(argv[1], "rb");
+  fseek(f, 0, SEEK_END); long sz = ftell(f); fseek(f, 0, SEEK_SET);
+  std::vector<unsigned char> buf(sz + 64, 0);
+  if (fread(buf.data(), 1, sz, f) != (size_t)sz) return 1;
+  fclose(f);
+  long n; memcpy(&n, buf.data(), 8);
+  const long long* off = reinterpret_cast<const long long*>(buf.data() + 8);
+  const unsigned char* pool = buf.data() + 8 + 8 * (n + 1);
+  FILE* o = fopen(argv[2], "wb");
+  for (long i = 0; i < n; ++i) {
+    unsigned long long h = txf::fingerprint64(pool + off[i], (uint32_t)(off[i + 1] - off[i]));
+    fwrite(&h, 8, 1, o);
+  }
+  fclose(o);
+  return 0;
+}
+''')
+    exe = tmp_path / "fp"
+    csrc = os.path.join(ROOT, "kubeflow-tfx-workshop_b200", "csrc")
+    subprocess.run(["nvcc", "-O2", "-std=c++17", "-I", csrc, "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
+    rng = np.random.default_rng(64)
+    lens = np.concatenate([rng.integers(33, 201, 80_000), rng.integers(33, 4097, 20_000), np.arange(33, 200)]).astype(np.int64)
+    lens = np.concatenate([lens, [64, 65, 127, 128, 129, 4096]])
+    # pool starts 8-byte aligned inside the file buffer: [n][offsets (n+1)][bytes]; pad so that it does
+    offsets = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    pool = rng.integers(0, 256, int(offsets[-1]), dtype=np.uint8)
+    (tmp_path / "in.bin").write_bytes(np.int64(len(lens)).tobytes() + offsets.tobytes() + pool.tobytes())
+    subprocess.run([str(exe), str(tmp_path / "in.bin"), str(tmp_path / "out.bin")], check=True)
+    got = np.fromfile(tmp_path / "out.bin", dtype=np.uint64)
+    want = O.fingerprint64_bulk(offsets.astype(np.int32), np.concatenate([pool, np.zeros(64, np.uint8)]))
+    assert got.shape == want.shape and np.array_equal(got, want)
+    for i in rng.integers(0, len(lens), 50):  # and the pure-Python restatement on a handful
+        assert int(got[i]) == O.fingerprint64(pool[offsets[i]:offsets[i + 1]].tobytes())
+
+
 def test_long_term_fingerprint_quality(tmp_path):
     """Avalanche and slice-collision statistics of the long-term fingerprint (vocab.cuh KeyMixer), on the
     host build of the header.  The fingerprint only pre-filters (matches are confirmed on the bytes), so
