@@ -131,6 +131,30 @@ TXF_API int txf_qresolve(const uint64_t* cells_dev, const uint32_t* edges_dev, c
 TXF_API int txf_qfinal(const uint32_t* direct_key_dev, const uint64_t* cand_rank_dev, const uint32_t* selected_key_dev,
                int ncols, int T, float* boundaries_dev, int32_t* nbound_dev, txf_stream_t stream);
 
+/* Quantile boundaries for MANY targets (num_buckets up to 1000 and more), two passes over the column
+ * (tft.bucketize analyzer, taxi_utils.py:128-130, at the sizes of BASELINE configs[4]):
+ *   edges_dev[ncols][E]: E <= 4096 sorted splitter keys (equi-depth order statistics of a sample, via txf_msel_*);
+ *   1. txf_qsplit_count   accumulates cells_dev[ncols][2E+1] (u64; cell 2p = strictly between splitter p-1 and p,
+ *                          2p+1 = equal to splitter p); shards / ranks merge by addition;
+ *   2. txf_qsplit_resolve  per target rank (ascending, 1-based; T <= 1024): the splitter it falls on (direct_key,
+ *                          cand_rank = 0) or its cell -- flagged in flags_dev[ncols][txf_qsplit_flag_words(E)] -- and
+ *                          its 1-based rank among all keys pass 2 will collect for the column; cand_total_dev[ncols];
+ *   3. txf_qsplit_collect  appends the keys of flagged cells to cand_dev[ncols][cand_cap] (cand_count_dev[ncols] keeps
+ *                          counting past cand_cap so that overflow is detectable);
+ *   4. txf_msel_* on the collected keys with cand_rank, then txf_qfinal as for the single-pass engine. */
+/* edges_dev[ncols][S] from sample_dev[ncols][M] (uint32 keys): S a power of two in [16, 4096], M >= 8 S */
+TXF_API int txf_qsplit_edges(const uint32_t* sample_dev, int ncols, int64_t M, int S, uint32_t* edges_dev, txf_stream_t stream);
+TXF_API size_t txf_qsplit_scratch_bytes(int ncols, int E);
+TXF_API size_t txf_qsplit_flag_words(int E);
+TXF_API int txf_qsplit_count(const void* const* values, const uint8_t* const* valid, const int32_t* dtype, int ncols,
+                             int64_t n, int E, const uint32_t* edges_dev, uint64_t* cells_dev, txf_stream_t stream);
+TXF_API int txf_qsplit_resolve(const uint64_t* cells_dev, const uint32_t* edges_dev, const uint64_t* target_ranks_dev,
+                               int ncols, int E, int T, uint32_t* direct_key_dev, uint64_t* cand_rank_dev,
+                               uint32_t* flags_dev, uint64_t* cand_total_dev, void* scratch_dev, txf_stream_t stream);
+TXF_API int txf_qsplit_collect(const void* const* values, const uint8_t* const* valid, const int32_t* dtype, int ncols,
+                               int64_t n, int E, const uint32_t* edges_dev, const uint32_t* flags_dev, uint32_t* cand_dev,
+                               uint64_t* cand_count_dev, int64_t cand_cap, txf_stream_t stream);
+
 /* ------------------------------------------------------------------------------------------
  * Vocabulary analyzer -- tft.compute_and_apply_vocabulary(top_k, num_oov_buckets)
  * (taxi_utils.py:121-126): exact occurrence counts in an open-addressing table keyed by the

@@ -92,6 +92,12 @@ _SIGNATURES = {
     "txf_qcount": (c_int, [_PP, _PP, POINTER(c_int32), c_int, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p]),
     "txf_qresolve": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "txf_qfinal": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "txf_qsplit_edges": (c_int, [c_void_p, c_int, c_int64, c_int, c_void_p, c_void_p]),
+    "txf_qsplit_scratch_bytes": (c_size_t, [c_int, c_int]),
+    "txf_qsplit_flag_words": (c_size_t, [c_int]),
+    "txf_qsplit_count": (c_int, [_PP, _PP, POINTER(c_int32), c_int, c_int64, c_int, c_void_p, c_void_p, c_void_p]),
+    "txf_qsplit_resolve": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "txf_qsplit_collect": (c_int, [_PP, _PP, POINTER(c_int32), c_int, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p]),
     "txf_vocab_table_bytes": (c_size_t, [c_int64]),
     "txf_vocab_lookup_bytes": (c_size_t, [c_int64]),
     "txf_vocab_sort_scratch_bytes": (c_size_t, [c_int64]),

@@ -498,6 +498,259 @@ __global__ void qfinal_kernel(const uint32_t* __restrict__ direct_key, const uin
   nbound[c] = m;
 }
 
+// --------------------------------------------------------------------------------------------
+// (3) splitter-select: exact order statistics for MANY targets (num_buckets 100 .. 1000) in two
+//     passes over the column.  One pass cannot do it: with T targets the brackets of the
+//     sample-select engine cover T * 10 sigma / M of the rows, i.e. everything once T reaches a few
+//     hundred.  Instead S (<= 4096) equi-depth splitters are taken from the sample; pass 1 counts,
+//     exactly, how many keys fall strictly between consecutive splitters and on each splitter
+//     (2S+1 cells, shared-memory atomics); the cell of every target rank is then known, and pass 2
+//     collects only the keys of those <= T cells (about T/S of the rows) for the final selection
+//     (txf_msel_* on the collected keys).  Cell counts are integers: shards and ranks merge by addition.
+// --------------------------------------------------------------------------------------------
+constexpr int kSpBlock = 512;
+constexpr int kSpLutBits = 12;
+constexpr int kSpMaxEdges = 4096;
+constexpr int kSpCandBuf = 4096;  // a 512-thread iteration adds at most 4096 keys... of which only flagged cells' keys land here
+
+struct SpLocator {  // shared-memory tables that map a key to its cell among E sorted edges (duplicates allowed)
+  const uint32_t* s_edges;  // [E]
+  const uint16_t* s_lut;    // [(1 << kSpLutBits) + 1]: number of edges below the start of each bin (last entry: E)
+  uint32_t first, last;
+  int shift, E;
+  // cell 2p = strictly between edge p-1 and edge p, 2p+1 = equal to edge p (first copy of a duplicated edge)
+  __device__ __forceinline__ int cell(uint32_t key) const {
+    if (key < first) return 0;
+    if (key > last) return 2 * E;
+    uint32_t bin = (key - first) >> shift;
+    int lo = s_lut[bin], hi = s_lut[bin + 1];
+    while (lo < hi) {  // lower_bound inside the bin's edge range (usually zero or one edge)
+      const int mid = (lo + hi) >> 1;
+      const bool lt = s_edges[mid] < key;
+      lo = lt ? mid + 1 : lo;
+      hi = lt ? hi : mid;
+    }
+    return 2 * lo + ((lo < E && s_edges[lo] == key) ? 1 : 0);
+  }
+};
+
+// builds the locator tables of column c in shared memory (all threads; ends with a barrier)
+__device__ __forceinline__ SpLocator sp_build(const uint32_t* __restrict__ edges, int E, uint32_t* s_edges, uint16_t* s_lut) {
+  for (int i = threadIdx.x; i < E; i += kSpBlock) s_edges[i] = edges[i];
+  __syncthreads();
+  SpLocator L;
+  L.s_edges = s_edges; L.s_lut = s_lut; L.E = E;
+  L.first = s_edges[0]; L.last = s_edges[E - 1];
+  const uint32_t span = L.last - L.first;
+  L.shift = span >> kSpLutBits ? 32 - kSpLutBits - __clz(span) : 0;
+  for (int j = threadIdx.x; j <= (1 << kSpLutBits); j += kSpBlock) {
+    const uint64_t lo_key = static_cast<uint64_t>(L.first) + (static_cast<uint64_t>(j) << L.shift);
+    int lo = 0, hi = E;  // number of edges below the bin start
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      const bool lt = s_edges[mid] < lo_key;
+      lo = lt ? mid + 1 : lo;
+      hi = lt ? hi : mid;
+    }
+    s_lut[j] = static_cast<uint16_t>(lo);
+  }
+  __syncthreads();
+  return L;
+}
+
+// Splitters: S distinct-as-far-as-possible equi-depth order statistics of the sample.  One CTA per column sorts a
+// strided subsample of 8 S keys in shared memory (bitonic), takes every 8th, drops repeated values and pads the
+// tail with the largest one (repeated splitters are harmless to the locator; they only have to be sorted).
+constexpr int kSeBlock = 1024;
+__global__ void __launch_bounds__(kSeBlock) qsplit_edges_kernel(const uint32_t* __restrict__ sample, int64_t M, int S,
+                                                                uint32_t* __restrict__ edges_all) {
+  extern __shared__ uint32_t se_s[];
+  const int c = blockIdx.x;
+  const int msub = 8 * S;
+  const uint32_t* src = sample + static_cast<size_t>(c) * M;
+  const int64_t stride = M / msub;
+  for (int i = threadIdx.x; i < msub; i += kSeBlock) se_s[i] = src[i * stride];
+  __syncthreads();
+  for (int k = 2; k <= msub; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int t = threadIdx.x; t < (msub >> 1); t += kSeBlock) {
+        const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));  // index with bit j clear
+        const int l = i | j;
+        const uint32_t a = se_s[i], b = se_s[l];
+        const bool up = (i & k) == 0;
+        if (up ? a > b : a < b) { se_s[i] = b; se_s[l] = a; }
+      }
+      __syncthreads();
+    }
+  }
+  uint32_t* edges = edges_all + static_cast<size_t>(c) * S;
+  if (threadIdx.x == 0) {
+    int m = 0;
+    uint32_t last = 0;
+    for (int j = 0; j < S; ++j) {
+      const uint32_t v = se_s[8 * j + 4];
+      if (m == 0 || v != last) { edges[m++] = v; last = v; }
+    }
+    for (; m < S; ++m) edges[m] = last;
+  }
+}
+
+// MODE 0: count cells.  MODE 1: append the keys whose cell is flagged to the candidate list.
+template <int MODE>
+__global__ void __launch_bounds__(kSpBlock) qsplit_kernel(NumColsView cols, int64_t n, int E, const uint32_t* __restrict__ edges_all,
+                                                          unsigned long long* __restrict__ cells_all,
+                                                          const uint32_t* __restrict__ flags_all, uint32_t* __restrict__ cand_all,
+                                                          unsigned long long* __restrict__ cand_count, int64_t cand_cap) {
+  extern __shared__ uint32_t sp_smem[];
+  __shared__ uint32_t s_ncand;
+  __shared__ unsigned long long s_base;
+  const int c = blockIdx.y;
+  const int ncell = 2 * E + 1;
+  uint32_t* s_edges = sp_smem;                                             // [E]
+  uint16_t* s_lut = reinterpret_cast<uint16_t*>(s_edges + E);              // [(1 << bits) + 1], padded to 4 bytes
+  uint32_t* s_aux = reinterpret_cast<uint32_t*>(s_lut + (1 << kSpLutBits) + 2);  // MODE 0: counters [ncell]; MODE 1: flag words + buffer
+  const SpLocator L = sp_build(edges_all + static_cast<size_t>(c) * E, E, s_edges, s_lut);
+  const int nflag = (ncell + 31) / 32;
+  if (MODE == 0) {
+    for (int i = threadIdx.x; i < ncell; i += kSpBlock) s_aux[i] = 0;
+  } else {
+    for (int i = threadIdx.x; i < nflag; i += kSpBlock) s_aux[i] = flags_all[static_cast<size_t>(c) * nflag + i];
+    if (threadIdx.x == 0) s_ncand = 0;
+  }
+  __syncthreads();
+  uint32_t* s_cand = s_aux + nflag;  // MODE 1
+  uint32_t* cand = cand_all + static_cast<size_t>(c) * cand_cap;
+  auto flush = [&]() {  // MODE 1, all threads
+    __syncthreads();
+    if (threadIdx.x == 0) s_base = atomicAdd(&cand_count[c], static_cast<unsigned long long>(s_ncand < kSpCandBuf ? s_ncand : kSpCandBuf));
+    __syncthreads();
+    const uint32_t m = s_ncand < kSpCandBuf ? s_ncand : kSpCandBuf;
+    for (uint32_t i = threadIdx.x; i < m; i += kSpBlock) {
+      const unsigned long long pos = s_base + i;
+      if (pos < static_cast<unsigned long long>(cand_cap)) cand[pos] = s_cand[i];
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) s_ncand = 0;
+    __syncthreads();
+  };
+  auto visit = [&](uint32_t key) {
+    const int cell = L.cell(key);
+    if (MODE == 0) {
+      atomicAdd(&s_aux[cell], 1u);
+    } else if ((s_aux[cell >> 5] >> (cell & 31)) & 1u) {
+      const uint32_t pos = atomicAdd(&s_ncand, 1u);
+      if (pos < kSpCandBuf) {
+        s_cand[pos] = key;
+      } else {  // CTA buffer full between two flushes: append to the global list directly
+        const unsigned long long g = atomicAdd(&cand_count[c], 1ULL);
+        if (g < static_cast<unsigned long long>(cand_cap)) cand[g] = key;
+      }
+    }
+  };
+  // quads interleaved over the grid; the candidate buffer is drained every few iterations (block-uniform trip count)
+  const void* values = cols.values[c];
+  const uint8_t* __restrict__ valid = cols.valid[c];
+  const bool f32 = cols.dtype[c] == TXF_F32;
+  const int64_t nquads = n >> 2;
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * kSpBlock;
+  const int64_t iters = (nquads + 2 * stride - 1) / (2 * stride);
+  for (int64_t it = 0; it < iters; ++it) {  // two quads per thread and iteration: both loads are issued before either is used
+    const int64_t qa = 2 * it * stride + blockIdx.x * static_cast<int64_t>(kSpBlock) + threadIdx.x, qb = qa + stride;
+    float4 xa = make_float4(0, 0, 0, 0), xb = xa;
+    uint32_t ma = 0, mb = 0;
+    if (qa < nquads) { xa = f32 ? load_quad_as_f32<true>(values, qa) : load_quad_as_f32<false>(values, qa); ma = quad_valid(valid, 4 * qa); }
+    if (qb < nquads) { xb = f32 ? load_quad_as_f32<true>(values, qb) : load_quad_as_f32<false>(values, qb); mb = quad_valid(valid, 4 * qb); }
+    if (qa < nquads) {
+      visit(f32_key(ma & 1 ? xa.x : 0.f)); visit(f32_key(ma & 2 ? xa.y : 0.f)); visit(f32_key(ma & 4 ? xa.z : 0.f)); visit(f32_key(ma & 8 ? xa.w : 0.f));
+    }
+    if (qb < nquads) {
+      visit(f32_key(mb & 1 ? xb.x : 0.f)); visit(f32_key(mb & 2 ? xb.y : 0.f)); visit(f32_key(mb & 4 ? xb.z : 0.f)); visit(f32_key(mb & 8 ? xb.w : 0.f));
+    }
+    if (MODE == 1 && __syncthreads_or(s_ncand > kSpCandBuf / 2)) flush();
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {  // rows past the last full quad
+    const int64_t i = (nquads << 2) + threadIdx.x;
+    const bool present = row_valid(valid, i);
+    visit(f32 ? cell_key_f32(static_cast<const float*>(values)[i], present) : cell_key_i64(static_cast<const long long*>(values)[i], present));
+  }
+  if (MODE == 1) {
+    flush();
+  } else {
+    __syncthreads();
+    for (int i = threadIdx.x; i < ncell; i += kSpBlock) {
+      const uint32_t v = s_aux[i];
+      if (v) atomicAdd(&cells_all[static_cast<size_t>(c) * ncell + i], static_cast<unsigned long long>(v));
+    }
+  }
+}
+
+// One CTA per column: prefix sums over the cells, then per target rank either the splitter it falls on (direct) or
+// its cell (flagged for pass 2) and its rank among all collected keys of the column (cells are in key order, so the
+// collected keys of earlier flagged cells precede those of later ones).
+__global__ void __launch_bounds__(1024) qsplit_resolve_kernel(const unsigned long long* __restrict__ cells_all,
+                                                              const uint32_t* __restrict__ edges_all, const uint64_t* __restrict__ ranks,
+                                                              int E, int T, uint32_t* __restrict__ direct_key,
+                                                              uint64_t* __restrict__ cand_rank, uint32_t* __restrict__ flags_all,
+                                                              unsigned long long* __restrict__ cand_total, unsigned long long* scratch) {
+  const int c = blockIdx.x;
+  const int ncell = 2 * E + 1, nflag = (ncell + 31) / 32;
+  const unsigned long long* cells = cells_all + static_cast<size_t>(c) * ncell;
+  unsigned long long* incl = scratch + static_cast<size_t>(c) * 2 * ncell;   // inclusive prefix of the cell counts
+  unsigned long long* fincl = incl + ncell;                                   // inclusive prefix of the FLAGGED cells' counts
+  uint32_t* flags = flags_all + static_cast<size_t>(c) * nflag;
+  __shared__ unsigned long long s_part[1024];
+  __shared__ int s_tcell[1024];  // cell of each target (T <= 1024 per launch chunk is enforced by the entry point)
+  const int per = (ncell + 1023) / 1024;
+  auto block_scan = [&](auto value_of, unsigned long long* out) {
+    const int b0 = threadIdx.x * per;
+    unsigned long long sum = 0;
+    for (int i = b0; i < b0 + per && i < ncell; ++i) sum += value_of(i);
+    s_part[threadIdx.x] = sum;
+    __syncthreads();
+    for (int off = 1; off < 1024; off <<= 1) {
+      unsigned long long v = threadIdx.x >= off ? s_part[threadIdx.x - off] : 0;
+      __syncthreads();
+      s_part[threadIdx.x] += v;
+      __syncthreads();
+    }
+    unsigned long long run = threadIdx.x ? s_part[threadIdx.x - 1] : 0;
+    for (int i = b0; i < b0 + per && i < ncell; ++i) { run += value_of(i); out[i] = run; }
+    __syncthreads();
+  };
+  block_scan([&](int i) { return cells[i]; }, incl);
+  for (int i = threadIdx.x; i < nflag; i += 1024) flags[i] = 0;
+  __syncthreads();
+  const uint32_t* edges = edges_all + static_cast<size_t>(c) * E;
+  for (int i = threadIdx.x; i < T; i += 1024) {
+    const unsigned long long r = ranks[i];  // 1-based
+    int lo = 0, hi = ncell - 1;             // first cell whose inclusive prefix reaches r
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (incl[mid] < r) lo = mid + 1; else hi = mid;
+    }
+    s_tcell[i] = lo;
+    if (lo & 1) {
+      direct_key[static_cast<size_t>(c) * T + i] = edges[lo >> 1];
+    } else {
+      direct_key[static_cast<size_t>(c) * T + i] = 0;
+      atomicOr(&flags[lo >> 5], 1u << (lo & 31));
+    }
+  }
+  __syncthreads();
+  block_scan([&](int i) { return ((flags[i >> 5] >> (i & 31)) & 1u) ? cells[i] : 0ULL; }, fincl);
+  for (int i = threadIdx.x; i < T; i += 1024) {
+    const int cell = s_tcell[i];
+    unsigned long long cr = 0;
+    if (!(cell & 1)) {
+      const unsigned long long before_cells = cell ? incl[cell - 1] : 0ULL;      // keys in all earlier cells
+      const unsigned long long before_cand = cell ? fincl[cell - 1] : 0ULL;      // collected keys in earlier flagged cells
+      cr = before_cand + (ranks[i] - before_cells);
+    }
+    cand_rank[static_cast<size_t>(c) * T + i] = cr;
+  }
+  if (threadIdx.x == 0) cand_total[c] = fincl[ncell - 1];
+}
+
 static int fill_view(NumColsView& v, const void* const* values, const uint8_t* const* valid, const int32_t* dtype,
                      int ncols, const char* who, bool raw) {
   TXF_REQUIRE(ncols >= 1 && ncols <= TXF_MAX_COLS, "%s: ncols=%d out of [1,%d]", who, ncols, TXF_MAX_COLS);
@@ -637,6 +890,83 @@ int txf_qcount(const void* const* values, const uint8_t* const* valid, const int
     count_launch(1);
   }
   TXF_LAUNCH_CHECK();
+  return TXF_OK;
+}
+
+size_t txf_qsplit_scratch_bytes(int ncols, int E) { return static_cast<size_t>(ncols) * 2 * (2 * static_cast<size_t>(E) + 1) * sizeof(uint64_t); }
+size_t txf_qsplit_flag_words(int E) { return (2 * static_cast<size_t>(E) + 1 + 31) / 32; }
+
+static int qsplit_launch(int mode, const void* const* values, const uint8_t* const* valid, const int32_t* dtype, int ncols, int64_t n, int E,
+                         const uint32_t* edges_dev, uint64_t* cells_dev, const uint32_t* flags_dev, uint32_t* cand_dev,
+                         uint64_t* cand_count_dev, int64_t cand_cap, txf_stream_t stream) {
+  using namespace txf;
+  TXF_REQUIRE(E >= 1 && E <= kSpMaxEdges, "qsplit: E=%d out of [1,%d]", E, kSpMaxEdges);
+  TXF_REQUIRE(n >= 0 && n < (1LL << 31), "qsplit: n out of range");
+  TXF_REQUIRE(edges_dev != nullptr, "qsplit: null edges");
+  if (n == 0) return TXF_OK;
+  NumColsView v{};
+  int rc = fill_view(v, values, valid, dtype, ncols, "qsplit", false);
+  if (rc) return rc;
+  const size_t ncell = 2 * static_cast<size_t>(E) + 1;
+  const size_t aux = mode == 0 ? ncell * 4 : ((ncell + 31) / 32) * 4 + kSpCandBuf * 4;
+  const size_t smem = static_cast<size_t>(E) * 4 + ((1 << kSpLutBits) + 2) * 2 + aux;
+  int per_sm = static_cast<int>((200 * 1024) / (smem + 1024));
+  per_sm = per_sm < 1 ? 1 : (per_sm > 6 ? 6 : per_sm);
+  dim3 grid(stream_grid(n, kSpBlock, per_sm, ncols), ncols);
+  cudaStream_t cs = static_cast<cudaStream_t>(stream);
+  if (mode == 0) {
+    TXF_REQUIRE(cells_dev != nullptr, "qsplit_count: null cells");
+    TXF_CUDA(cudaFuncSetAttribute(qsplit_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    qsplit_kernel<0><<<grid, kSpBlock, smem, cs>>>(v, n, E, edges_dev, reinterpret_cast<unsigned long long*>(cells_dev), nullptr, nullptr,
+                                                   nullptr, 0);
+  } else {
+    TXF_REQUIRE(flags_dev && cand_dev && cand_count_dev && cand_cap >= 1, "qsplit_collect: null pointer / empty candidate buffer");
+    TXF_CUDA(cudaFuncSetAttribute(qsplit_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    qsplit_kernel<1><<<grid, kSpBlock, smem, cs>>>(v, n, E, edges_dev, nullptr, flags_dev, cand_dev,
+                                                   reinterpret_cast<unsigned long long*>(cand_count_dev), cand_cap);
+  }
+  TXF_LAUNCH_CHECK();
+  count_launch(1);
+  return TXF_OK;
+}
+
+int txf_qsplit_edges(const uint32_t* sample_dev, int ncols, int64_t M, int S, uint32_t* edges_dev, txf_stream_t stream) {
+  using namespace txf;
+  TXF_REQUIRE(ncols >= 1 && ncols <= TXF_MAX_COLS, "qsplit_edges: ncols out of range");
+  TXF_REQUIRE(S >= 16 && S <= kSpMaxEdges && (S & (S - 1)) == 0, "qsplit_edges: S must be a power of two in [16,%d]", kSpMaxEdges);
+  TXF_REQUIRE(M >= 8LL * S, "qsplit_edges: the sample must hold at least 8 S keys per column");
+  TXF_REQUIRE(sample_dev && edges_dev, "qsplit_edges: null pointer");
+  const int smem = 8 * S * 4;
+  TXF_CUDA(cudaFuncSetAttribute(qsplit_edges_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  qsplit_edges_kernel<<<ncols, kSeBlock, smem, static_cast<cudaStream_t>(stream)>>>(sample_dev, M, S, edges_dev);
+  TXF_LAUNCH_CHECK();
+  count_launch(1);
+  return TXF_OK;
+}
+
+int txf_qsplit_count(const void* const* values, const uint8_t* const* valid, const int32_t* dtype, int ncols, int64_t n, int E,
+                     const uint32_t* edges_dev, uint64_t* cells_dev, txf_stream_t stream) {
+  return qsplit_launch(0, values, valid, dtype, ncols, n, E, edges_dev, cells_dev, nullptr, nullptr, nullptr, 0, stream);
+}
+
+int txf_qsplit_collect(const void* const* values, const uint8_t* const* valid, const int32_t* dtype, int ncols, int64_t n, int E,
+                       const uint32_t* edges_dev, const uint32_t* flags_dev, uint32_t* cand_dev, uint64_t* cand_count_dev,
+                       int64_t cand_cap, txf_stream_t stream) {
+  return qsplit_launch(1, values, valid, dtype, ncols, n, E, edges_dev, nullptr, flags_dev, cand_dev, cand_count_dev, cand_cap, stream);
+}
+
+int txf_qsplit_resolve(const uint64_t* cells_dev, const uint32_t* edges_dev, const uint64_t* target_ranks_dev, int ncols, int E, int T,
+                       uint32_t* direct_key_dev, uint64_t* cand_rank_dev, uint32_t* flags_dev, uint64_t* cand_total_dev,
+                       void* scratch_dev, txf_stream_t stream) {
+  using namespace txf;
+  TXF_REQUIRE(ncols >= 1 && ncols <= TXF_MAX_COLS && E >= 1 && E <= kSpMaxEdges && T >= 1 && T <= 1024, "qsplit_resolve: bad sizes");
+  TXF_REQUIRE(cells_dev && edges_dev && target_ranks_dev && direct_key_dev && cand_rank_dev && flags_dev && cand_total_dev && scratch_dev,
+              "qsplit_resolve: null pointer");
+  qsplit_resolve_kernel<<<ncols, 1024, 0, static_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const unsigned long long*>(cells_dev), edges_dev, target_ranks_dev, E, T, direct_key_dev, cand_rank_dev, flags_dev,
+      reinterpret_cast<unsigned long long*>(cand_total_dev), static_cast<unsigned long long*>(scratch_dev));
+  TXF_LAUNCH_CHECK();
+  count_launch(1);
   return TXF_OK;
 }
 

@@ -18,6 +18,8 @@
 // Ranking reproduces tft: drop '' and terms containing \n / \r, order by (count, bytes)
 // descending, keep top_k.
 // Algorithmic bytes of the count pass: 4 (offset) + term bytes per row + 1 validity bit.
+#include <cstdlib>
+
 #include "vocab.cuh"
 #include "str_pipe.cuh"
 
@@ -674,6 +676,10 @@ int txf_vocab_count(const int32_t* offsets_dev, const uint8_t* pool_dev, const u
   const int warps = cta_warps == 0 ? kVcWarpsFull : cta_warps;
   int64_t want = (n + static_cast<int64_t>(kVcStepRows) * warps - 1) / (static_cast<int64_t>(kVcStepRows) * warps);
   int grid = static_cast<int>(want < kVcGrid ? want : kVcGrid);
+  if (const char* e = getenv("TXF_PERSISTENT_CTAS")) {  // experiment knob: leave some SMs free of the persistent kernels
+    const int lim = atoi(e);
+    if (lim >= 1 && lim < grid) grid = lim;
+  }
   auto launch = [&](auto kernel, int w) -> int {
     TXF_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(vc_smem_bytes(w))));
     TXF_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));

@@ -200,6 +200,8 @@ class Engine:
         self.seed = int(seed)
         self._ws: Dict[Tuple, torch.Tensor] = {}
         self.force_general_quantiles = False
+        self.split_quantiles = True          # many targets: two passes over equi-depth splitters instead of the 4-pass radix select
+        self.force_split_quantiles = False   # (tests) take the two-pass engine even where one pass would do
         self.use_codes = True   # analyze writes dictionary codes; transform of the same table decodes them
         self.overlap_streams = True
         self._side = None
@@ -372,8 +374,9 @@ class Engine:
         if self.overlap_streams:
             with torch.cuda.stream(sq):
                 pending_q = {nb: self._quantiles_sample(nb, keys, chunks, n_locals) for nb, keys in self.bucket_groups.items()}
+            wait_gather = os.environ.get("TXF_NO_GATHER_WAIT") != "1"  # experiment knob
             if side_work is not None:
-                side_work([pq["gathered"] for pq in pending_q.values() if pq.get("gathered") is not None])
+                side_work([pq["gathered"] for pq in pending_q.values() if pq.get("gathered") is not None] if wait_gather else [])
                 side_work = None
             if pending_v is None:
                 # Row counts came from the caller, so nothing made the host wait above.  The count pass is queued right BEHIND
@@ -381,7 +384,7 @@ class Engine:
                 # millisecond to enqueue): a collective kernel cannot become resident once the persistent count CTAs (plus the
                 # stream kernel) hold every SM's registers, and the quantile pass would wait for the whole count pass.
                 for pq in pending_q.values():
-                    if pq.get("gathered") is not None:
+                    if pq.get("gathered") is not None and wait_gather:
                         sv.wait_event(pq["gathered"])
                 with torch.cuda.stream(sv):
                     pending_v = count_vocab()
@@ -550,7 +553,7 @@ class Engine:
         if T < 1 or n_total == 0:
             return pend
         M_total = min(self.sample_size, n_total // 8)
-        if self.force_general_quantiles or T > nat.TXF_QMAX_TARGETS or n_total < (1 << 18) or M_total < 1024 * T:
+        if self.force_general_quantiles or n_total < (1 << 18) or M_total < (1 << 12) or T > 1024:
             return pend
         # per-rank sample sizes, proportional to the rows each rank holds (host arithmetic, no sync)
         M_ranks = [(M_total * nl) // n_total for nl in n_locals]
@@ -562,8 +565,13 @@ class Engine:
             k = min(max(math.ceil(q * M_sum), 1), M_sum)
             d = int(math.ceil(self.bracket_sigmas * math.sqrt(M_sum * q * (1.0 - q)))) + 2
             edges_ranks += [max(1, k - d), min(M_sum, k + d)]
-        if any(b < a for a, b in zip(edges_ranks, edges_ranks[1:])):
-            return pend  # brackets would overlap: too many targets for this sample
+        # one pass (brackets around every target) while the brackets are few and disjoint; otherwise two passes over
+        # equi-depth splitters (with T targets the brackets cover about 10 T sigma / M of the rows: everything for T in the hundreds)
+        pend["mode"] = "bracket"
+        if T > nat.TXF_QMAX_TARGETS or M_total < 1024 * T or any(b < a for a, b in zip(edges_ranks, edges_ranks[1:])) or self.force_split_quantiles:
+            if not self.split_quantiles:
+                return pend
+            pend["mode"] = "split"
         s = self._stream()
         # (1) sample, chunk by chunk
         M_local = M_ranks[self.comm.rank]
@@ -608,6 +616,8 @@ class Engine:
         ncols = len(keys)
         s = self._stream()
         M_sum = sample.shape[1]
+        if pend["mode"] == "split":
+            return self._quantiles_split(nb, pend, chunks, sample, ranks, n_local)
         # (2) bracket edges = exact order statistics of the sample
         er = self._host_const([edges_ranks] * ncols, torch.int64)
         sptrs = nat.ptr_array([sample[c].data_ptr() for c in range(ncols)])
@@ -632,6 +642,55 @@ class Engine:
         pend.update(fast=True, edges=edges, cells=cells, cand=cand, cand_count=cand_count, cand_cap=cand_cap, ranks=ranks)
         if not self.comm.active:
             self._quantiles_resolve(nb, pend)
+        return pend
+
+    def _quantiles_split(self, nb: int, pend, chunks, sample: torch.Tensor, ranks: List[int], n_local: int):
+        """Two passes for many targets (txf_qsplit_*): S equi-depth splitters from the sample, exact cell counts, then
+        only the keys of the <= T target cells are collected for the final selection.  Multi-rank: the cell counts are
+        all-reduced and the selection all-reduces its histograms; the collected keys stay where they are."""
+        keys, T = pend["keys"], pend["T"]
+        ncols = len(keys)
+        s = self._stream()
+        M_sum = sample.shape[1]
+        S = 4096
+        while 8 * S > M_sum:  # the splitter kernel sorts a subsample of 8 S keys per column in shared memory
+            S >>= 1
+        edges = self._buf(f"q{nb}_sp_edges", (ncols, S), torch.int32)
+        nat.call("txf_qsplit_edges", sample.data_ptr(), ncols, M_sum, S, edges.data_ptr(), s)
+        cells = self._buf(f"q{nb}_sp_cells", (ncols, 2 * S + 1), torch.int64, zero=True)
+        args = [self._num_args([ch[k] for k in keys]) + (len(ch),) for ch in chunks if len(ch)]
+        for v, m, d, n in args:
+            nat.call("txf_qsplit_count", v, m, d, ncols, n, S, edges.data_ptr(), cells.data_ptr(), s)
+        if self.comm.active:
+            self.comm.all_reduce_sum_(cells)
+        ranks_dev = self._host_const(ranks, torch.int64)
+        direct = self._buf(f"q{nb}_direct", (ncols, T), torch.int32)
+        cand_rank = self._buf(f"q{nb}_cand_rank", (ncols, T), torch.int64)
+        flags = self._buf(f"q{nb}_sp_flags", (ncols, nat.query("txf_qsplit_flag_words", S)), torch.int32)
+        cand_total = self._buf(f"q{nb}_sp_total", (ncols,), torch.int64)
+        scratch = self._buf(f"q{nb}_sp_scratch", nat.query("txf_qsplit_scratch_bytes", ncols, S), torch.uint8)
+        nat.call("txf_qsplit_resolve", cells.data_ptr(), edges.data_ptr(), ranks_dev.data_ptr(), ncols, S, T, direct.data_ptr(),
+                 cand_rank.data_ptr(), flags.data_ptr(), cand_total.data_ptr(), scratch.data_ptr(), s)
+        # a target cell holds about n / (S + 1) keys (heavy duplicates sit ON splitters and are answered directly)
+        cand_cap = max(1 << 16, min(int(3.0 * min(T, S + 1) / (S + 1) * n_local) + 65536, max(n_local, 1)))
+        cand = self._buf(f"q{nb}_cand", (ncols, cand_cap), torch.int32)
+        cand_count = self._buf(f"q{nb}_cand_count", (ncols,), torch.int64, zero=True)
+        for v, m, d, n in args:
+            nat.call("txf_qsplit_collect", v, m, d, ncols, n, S, edges.data_ptr(), flags.data_ptr(), cand.data_ptr(),
+                     cand_count.data_ptr(), cand_cap, s)
+        status = (cand_count > cand_cap).to(torch.int32)  # overflow of the collected-key buffer: the general engine takes over
+        if self.comm.active:
+            self.comm.all_reduce_max_(status)
+        cptrs = nat.ptr_array([cand[c].data_ptr() for c in range(ncols)])
+
+        def cand_pass(st, p):
+            nat.call("txf_msel_hist", st, ncols, T, p, cptrs, None, None, 1, cand.shape[1], cand_count.data_ptr(), s)
+
+        sel = self._msel(f"q{nb}_sel", ncols, T, cand_rank, cand_pass, reduce=self.comm.active)
+        bounds = self._buf(f"q{nb}_bounds", (ncols, T), torch.float32)
+        nbound = self._buf(f"q{nb}_nbound", (ncols,), torch.int32)
+        nat.call("txf_qfinal", direct.data_ptr(), cand_rank.data_ptr(), sel.data_ptr(), ncols, T, bounds.data_ptr(), nbound.data_ptr(), s)
+        pend.update(split_done=True, status=status, bounds=bounds, nbound=nbound)
         return pend
 
     def _quantiles_resolve(self, nb: int, pend, global_count: Optional[torch.Tensor] = None):
@@ -873,11 +932,12 @@ class Engine:
             self.last_quantile_path[nb] = "empty"
             return BucketResult(list(keys), nb, torch.zeros((ncols, max(T, 1)), dtype=torch.float32, device=self.device),
                                 torch.zeros((ncols,), dtype=torch.int32, device=self.device), path="empty")
-        if pend["fast"]:
+        if pend["fast"] or pend.get("split_done"):
             status = pend["status"].cpu()
             if int(status.abs().sum()) == 0:
-                self.last_quantile_path[nb] = "sample-select"
-                return BucketResult(list(keys), nb, pend["bounds"], pend["nbound"], path="sample-select")
+                path = "sample-select" if pend["fast"] else "splitter-select"
+                self.last_quantile_path[nb] = path
+                return BucketResult(list(keys), nb, pend["bounds"], pend["nbound"], path=path)
         self.last_quantile_path[nb] = "radix-select"
         return self._quantiles_general(nb, keys, chunks, n_total)
 

@@ -314,18 +314,21 @@ def test_bucketize_stress(ktw, nb):
     if nb <= 33:
         assert eng.last_quantile_path[nb] == "sample-select"
     if nb >= 100:
-        assert eng.last_quantile_path[nb] == "radix-select"
+        assert eng.last_quantile_path[nb] == "splitter-select"
     for k in keys:
         filled = O.fill_in_missing(cols[k])
         want_b = O.quantile_boundaries(filled, nb)
         got_b = res.boundaries_of(k)
         assert np.array_equal(got_b.view(np.uint32), want_b.view(np.uint32)), (k, nb, got_b[:5], want_b[:5])
         assert np.array_equal(out[k + "_b"].values.cpu().numpy(), O.bucketize(filled, want_b)), (k, nb)
-    # the general engine returns the same boundaries
-    eng.force_general_quantiles = True
-    state2 = eng.analyze(dev)
-    for k in keys:
-        assert np.array_equal(state2.buckets[nb].boundaries_of(k).view(np.uint32), O.quantile_boundaries(O.fill_in_missing(cols[k]), nb).view(np.uint32)), k
+    # the general engine and the two-pass splitter engine return the same boundaries
+    for attr in ("force_general_quantiles", "force_split_quantiles"):
+        setattr(eng, attr, True)
+        state2 = eng.analyze(dev)
+        setattr(eng, attr, False)
+        assert eng.last_quantile_path[nb] == ("radix-select" if attr == "force_general_quantiles" else "splitter-select"), (attr, eng.last_quantile_path)
+        for k in keys:
+            assert np.array_equal(state2.buckets[nb].boundaries_of(k).view(np.uint32), O.quantile_boundaries(O.fill_in_missing(cols[k]), nb).view(np.uint32)), (k, attr)
 
 
 def test_bucketize_nan_goes_last(ktw):
