@@ -126,6 +126,16 @@ TXF_API int txf_qresolve(const uint64_t* cells_dev, const uint32_t* edges_dev, c
                  int64_t cand_cap, const uint64_t* target_ranks_dev, int ncols, int T,
                  uint32_t* direct_key_dev, uint64_t* cand_rank_dev, int32_t* status_dev,
                  txf_stream_t stream);
+/* Selection among the candidates in ONE histogram pass (instead of txf_msel_*'s four): the candidates of bracket p
+ * are counted by (key - lower edge - 1) into B bins of hist_dev (u32 [ncols][T][B], then [ncols] overflow words;
+ * txf_bsel_hist zeroes it).  Shards / ranks merge by adding hist_dev.  txf_bsel_resolve then writes the selected
+ * keys; a column whose bracket spans more than B keys gets status bit 4 (use txf_msel_* on its candidates instead). */
+TXF_API size_t txf_bsel_hist_bytes(int ncols, int T, int B);
+TXF_API int txf_bsel_hist(const uint32_t* cand_dev, int64_t cand_cap, const uint64_t* cand_count_dev, const uint32_t* edges_dev,
+                          int ncols, int T, int B, uint32_t* hist_dev, txf_stream_t stream);
+TXF_API int txf_bsel_resolve(const uint32_t* hist_dev, const uint64_t* cells_dev, const uint32_t* edges_dev,
+                             const uint64_t* cand_rank_dev, int ncols, int T, int B, uint32_t* selected_key_dev,
+                             int32_t* status_dev, txf_stream_t stream);
 /* keys (direct where cand_rank == 0, else selected) -> distinct fp32 boundaries
  * boundaries_dev[ncols][T], nbound_dev[ncols] */
 TXF_API int txf_qfinal(const uint32_t* direct_key_dev, const uint64_t* cand_rank_dev, const uint32_t* selected_key_dev,

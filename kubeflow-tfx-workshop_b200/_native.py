@@ -91,6 +91,9 @@ _SIGNATURES = {
     "txf_qsample": (c_int, [_PP, _PP, POINTER(c_int32), c_int, c_int64, c_int64, c_uint64, c_void_p, c_void_p]),
     "txf_qcount": (c_int, [_PP, _PP, POINTER(c_int32), c_int, c_int64, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p]),
     "txf_qresolve": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "txf_bsel_hist_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "txf_bsel_hist": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "txf_bsel_resolve": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "txf_qfinal": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "txf_qsplit_edges": (c_int, [c_void_p, c_int, c_int64, c_int, c_void_p, c_void_p]),
     "txf_qsplit_scratch_bytes": (c_size_t, [c_int, c_int]),

@@ -480,6 +480,114 @@ __global__ void qresolve_kernel(const unsigned long long* __restrict__ cells_all
   if (threadIdx.x == 0) status[c] = bad;
 }
 
+// --------------------------------------------------------------------------------------------
+// Bracket select: the exact order statistic inside each bracket from ONE histogram of the candidates.
+// A bracket [lo, hi] around a target is narrow in KEY space on real columns (a handful of distinct
+// values between two order statistics of the sample that are 0.5 % of the rows apart), so the candidate
+// keys of bracket p are histogrammed by (key - lo - 1) into B bins; if every bracket spans at most B keys
+// the histogram IS the exact distribution and one prefix scan finds the target -- one integer sum to merge
+// across ranks instead of the four dependent digit passes of the radix select.  A wider bracket raises the
+// column's overflow word and the caller falls back to txf_msel_* on the candidates.
+// hist layout (u32): [ncols][T][B] counts, then [ncols] overflow words.
+// --------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) bsel_hist_kernel(const uint32_t* __restrict__ cand_all, int64_t cand_cap,
+                                                        const unsigned long long* __restrict__ cand_count,
+                                                        const uint32_t* __restrict__ edges_all, int ncols, int T, int B,
+                                                        uint32_t* __restrict__ hist) {
+  extern __shared__ uint32_t bs_edges[];  // [2T]
+  // Columns with few distinct values (centroids) send all candidates of a bracket to a handful of bins: counted with
+  // global atomics they would serialise on those addresses.  A small CTA-local table absorbs them (open addressing,
+  // 4 probes); bins that do not fit go to the global histogram directly -- fine-grained columns spread out anyway.
+  constexpr int kSlots = 1024;
+  __shared__ uint32_t s_key[kSlots], s_cnt[kSlots];
+  const int c = blockIdx.y;
+  const int E = 2 * T;
+  for (int i = threadIdx.x; i < E; i += 256) bs_edges[i] = edges_all[static_cast<size_t>(c) * E + i];
+  for (int i = threadIdx.x; i < kSlots; i += 256) { s_key[i] = 0xFFFFFFFFu; s_cnt[i] = 0; }
+  __syncthreads();
+  const unsigned long long have = cand_count[c];
+  const int64_t m = have < static_cast<unsigned long long>(cand_cap) ? static_cast<int64_t>(have) : cand_cap;
+  const uint32_t* cand = cand_all + static_cast<size_t>(c) * cand_cap;
+  uint32_t* h = hist + static_cast<size_t>(c) * T * B;
+  uint32_t* over = hist + static_cast<size_t>(ncols) * T * B + c;
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * 256;
+  for (int64_t i = blockIdx.x * 256LL + threadIdx.x; i < m; i += stride) {
+    const uint32_t key = cand[i];
+    int lo = 0, len = E;  // number of edges strictly below the key
+    while (len > 0) {
+      const int half = len >> 1;
+      const bool lt = bs_edges[lo + half] < key;
+      lo = lt ? lo + half + 1 : lo;
+      len = lt ? len - half - 1 : half;
+    }
+    const int p = (lo - 1) >> 1;  // candidates lie strictly inside a bracket: lo is odd
+    const uint32_t bin = key - bs_edges[2 * p] - 1u;
+    if (!(lo & 1) || bin >= static_cast<uint32_t>(B)) {
+      atomicOr(over, 1u);
+      continue;
+    }
+    const uint32_t idx = static_cast<uint32_t>(p) * static_cast<uint32_t>(B) + bin;
+    uint32_t slot = (idx * 2654435761u) >> 22;
+    bool placed = false;
+#pragma unroll
+    for (int probe = 0; probe < 4 && !placed; ++probe, slot = (slot + 1) & (kSlots - 1)) {
+      uint32_t cur = s_key[slot];
+      if (cur == 0xFFFFFFFFu) cur = atomicCAS(&s_key[slot], 0xFFFFFFFFu, idx);
+      if (cur == 0xFFFFFFFFu || cur == idx) { atomicAdd(&s_cnt[slot], 1u); placed = true; }
+    }
+    if (!placed) atomicAdd(&h[idx], 1u);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < kSlots; i += 256)
+    if (s_cnt[i]) atomicAdd(&h[s_key[i]], s_cnt[i]);
+}
+
+// one CTA per (target, column): rank of the target among its bracket's candidates -> bin -> key
+__global__ void __launch_bounds__(256) bsel_resolve_kernel(const uint32_t* __restrict__ hist, const unsigned long long* __restrict__ cells_all,
+                                                           const uint32_t* __restrict__ edges_all, const uint64_t* __restrict__ cand_rank,
+                                                           int ncols, int T, int B, uint32_t* __restrict__ selected,
+                                                           int32_t* __restrict__ status) {
+  const int p = blockIdx.x, c = blockIdx.y;
+  const int E = 2 * T, ncell = 2 * E + 1;
+  const size_t k = static_cast<size_t>(c) * T + p;
+  const uint64_t cr = cand_rank[k];
+  if (cr == 0) {  // answered by an edge
+    if (threadIdx.x == 0) selected[k] = 0;
+    return;
+  }
+  const uint32_t over = hist[static_cast<size_t>(ncols) * T * B + c];
+  if (over) {
+    if (threadIdx.x == 0) { selected[k] = 0; atomicOr(&status[c], 4); }
+    return;
+  }
+  const unsigned long long* cells = cells_all + static_cast<size_t>(c) * ncell;
+  unsigned long long before = 0;  // candidates of earlier brackets precede this bracket's in key order
+  for (int q = 0; q < p; ++q) before += cells[2 * (2 * q + 1)];
+  const unsigned long long r = cr - before;  // 1-based rank inside the bracket
+  const uint32_t* h = hist + k * B;
+  __shared__ unsigned long long s_part[256];
+  const int per = (B + 255) / 256, b0 = threadIdx.x * per;
+  unsigned long long sum = 0;
+  for (int i = b0; i < b0 + per && i < B; ++i) sum += h[i];
+  s_part[threadIdx.x] = sum;
+  __syncthreads();
+  for (int off = 1; off < 256; off <<= 1) {
+    const unsigned long long v = threadIdx.x >= off ? s_part[threadIdx.x - off] : 0;
+    __syncthreads();
+    s_part[threadIdx.x] += v;
+    __syncthreads();
+  }
+  const unsigned long long excl = threadIdx.x ? s_part[threadIdx.x - 1] : 0;
+  if (r > excl && r <= s_part[threadIdx.x]) {  // exactly one thread owns the target
+    unsigned long long run = excl;
+    for (int i = b0; i < b0 + per && i < B; ++i) {
+      run += h[i];
+      if (r <= run) { selected[k] = edges_all[static_cast<size_t>(c) * E + 2 * p] + 1u + static_cast<uint32_t>(i); break; }
+    }
+  }
+  if (threadIdx.x == 255 && r > s_part[255]) atomicOr(&status[c], 8);  // fewer candidates than the rank: inconsistent counts
+}
+
 __global__ void qfinal_kernel(const uint32_t* __restrict__ direct_key, const uint64_t* __restrict__ cand_rank,
                               const uint32_t* __restrict__ selected, int ncols, int T, float* __restrict__ boundaries,
                               int32_t* __restrict__ nbound) {
@@ -981,6 +1089,41 @@ int txf_qresolve(const uint64_t* cells_dev, const uint32_t* edges_dev, const uin
       reinterpret_cast<const unsigned long long*>(cells_dev), edges_dev,
       reinterpret_cast<const unsigned long long*>(cand_count_dev), cand_cap, target_ranks_dev, ncols, T, direct_key_dev,
       cand_rank_dev, status_dev);
+  TXF_LAUNCH_CHECK();
+  count_launch(1);
+  return TXF_OK;
+}
+
+size_t txf_bsel_hist_bytes(int ncols, int T, int B) {
+  return (static_cast<size_t>(ncols) * T * B + ncols) * sizeof(uint32_t);
+}
+
+int txf_bsel_hist(const uint32_t* cand_dev, int64_t cand_cap, const uint64_t* cand_count_dev, const uint32_t* edges_dev, int ncols, int T,
+                  int B, uint32_t* hist_dev, txf_stream_t stream) {
+  using namespace txf;
+  TXF_REQUIRE(ncols >= 1 && ncols <= TXF_MAX_COLS && T >= 1 && T <= TXF_QMAX_TARGETS && B >= 16 && B <= (1 << 20), "bsel_hist: bad sizes");
+  TXF_REQUIRE(cand_dev && cand_count_dev && edges_dev && hist_dev && cand_cap >= 1, "bsel_hist: null pointer");
+  cudaStream_t cs = static_cast<cudaStream_t>(stream);
+  TXF_CUDA(cudaMemsetAsync(hist_dev, 0, txf_bsel_hist_bytes(ncols, T, B), cs));
+  int64_t blocks = (cand_cap + 255) / 256;
+  const int64_t cap = 4LL * kSMs * 8 / ncols + 1;
+  if (blocks > cap) blocks = cap;
+  dim3 grid(static_cast<unsigned>(blocks), ncols);
+  bsel_hist_kernel<<<grid, 256, 2 * T * sizeof(uint32_t), cs>>>(cand_dev, cand_cap, reinterpret_cast<const unsigned long long*>(cand_count_dev),
+                                                                edges_dev, ncols, T, B, hist_dev);
+  TXF_LAUNCH_CHECK();
+  count_launch(1);
+  return TXF_OK;
+}
+
+int txf_bsel_resolve(const uint32_t* hist_dev, const uint64_t* cells_dev, const uint32_t* edges_dev, const uint64_t* cand_rank_dev,
+                     int ncols, int T, int B, uint32_t* selected_key_dev, int32_t* status_dev, txf_stream_t stream) {
+  using namespace txf;
+  TXF_REQUIRE(ncols >= 1 && ncols <= TXF_MAX_COLS && T >= 1 && T <= TXF_QMAX_TARGETS && B >= 16, "bsel_resolve: bad sizes");
+  TXF_REQUIRE(hist_dev && cells_dev && edges_dev && cand_rank_dev && selected_key_dev && status_dev, "bsel_resolve: null pointer");
+  dim3 grid(T, ncols);
+  bsel_resolve_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(hist_dev, reinterpret_cast<const unsigned long long*>(cells_dev),
+                                                                         edges_dev, cand_rank_dev, ncols, T, B, selected_key_dev, status_dev);
   TXF_LAUNCH_CHECK();
   count_launch(1);
   return TXF_OK;

@@ -200,6 +200,8 @@ class Engine:
         self.seed = int(seed)
         self._ws: Dict[Tuple, torch.Tensor] = {}
         self.force_general_quantiles = False
+        self.bracket_select = True           # candidates: one bracket-histogram pass (falls back to radix digits when a bracket is wide)
+        self.last_quantile_select: Dict[int, str] = {}
         self.split_quantiles = True          # many targets: two passes over equi-depth splitters instead of the 4-pass radix select
         self.force_split_quantiles = False   # (tests) take the two-pass engine even where one pass would do
         self.use_codes = True   # analyze writes dictionary codes; transform of the same table decodes them
@@ -213,6 +215,8 @@ class Engine:
         self.last_vocab_exchange: Dict[str, str] = {}
         self.timeline: Dict[str, float] = {}   # TXF_PROFILE=1: wall ms per analyze() segment (with device syncs)
         self._profile = os.environ.get("TXF_PROFILE") == "1"
+        self._trace_on = os.environ.get("TXF_TRACE") == "1"
+        self.trace_events: List[Tuple[str, torch.cuda.Event]] = []
         self.last_quantile_path: Dict[int, str] = {}
 
         self.moment_keys: List[str] = []
@@ -268,6 +272,22 @@ class Engine:
             t = torch.tensor(data, dtype=dtype, device=self.device)
             self._host_consts[key] = t
         return t
+
+    def _mark(self, name: str, stream=None):
+        """TXF_TRACE=1: record a CUDA event on `stream` (default: current) -- a timeline without host syncs."""
+        if self._trace_on:
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record(stream if stream is not None else torch.cuda.current_stream())
+            self.trace_events.append((name, ev))
+
+    def trace_report(self) -> Dict[str, float]:
+        """ms from the first mark to every later one (call after a device synchronize)."""
+        if not self.trace_events:
+            return {}
+        t0 = self.trace_events[0][1]
+        out = {name: round(t0.elapsed_time(ev), 3) for name, ev in self.trace_events[1:]}
+        self.trace_events = []
+        return out
 
     def _tick(self, name: str):
         if self._profile:
@@ -341,6 +361,7 @@ class Engine:
             torch.cuda.synchronize(self.device)
             self._t0 = time.perf_counter()
         main = torch.cuda.current_stream()
+        self._mark("analyze_start")
         self._formatted.clear()
         # the three analyzer families are independent: queue them on three streams so that the
         # HBM-bound moments pass and the issue-bound counting passes share the SMs
@@ -388,12 +409,16 @@ class Engine:
                         sv.wait_event(pq["gathered"])
                 with torch.cuda.stream(sv):
                     pending_v = count_vocab()
+                    self._mark("vocab_counted")
             with torch.cuda.stream(sq):
                 pending_q = {nb: self._quantiles_count(nb, pq, chunks) for nb, pq in pending_q.items()}
+                self._mark("quantiles_counted")
             self._analyze_moments(chunks, state, defer)
             self._analyze_minmax(chunks, state, defer)
+            self._mark("moments_done")
             main.wait_stream(sv)
             main.wait_stream(sq)
+            self._mark("local_pass_done")
         else:
             if side_work is not None:
                 side_work([])
@@ -404,7 +429,7 @@ class Engine:
         if self.comm.active and self.fixed_exchange and not self._profile:
             # the fixed-layout exchange needs no value from the host: queue it behind the local pass
             # so that its launches are issued while the GPU is still busy, then wait once
-            self._exchange_fixed(pending_q, pending_v, state)
+            self._exchange_fixed(pending_q, pending_v, state, (lambda st: between(st, "moments")) if between is not None else None)
             main.synchronize()
         else:
             # one host round trip: everything queued above has to finish before sizes/flags are read
@@ -421,7 +446,7 @@ class Engine:
         self._tick("quantiles_finish")
         rank_stream = main
         if between is not None and self.overlap_streams and pending_v:
-            between(state)
+            between(state, "boundaries")
             rank_stream = self._side[1]  # everything queued so far has completed (host sync above): no event needed to start
         with torch.cuda.stream(rank_stream):
             for vk, pend in pending_v.items():
@@ -432,6 +457,7 @@ class Engine:
                         break
         if rank_stream is not main:
             main.wait_stream(rank_stream)
+        self._mark("analyze_done")
         self._tick("vocab_finish")
         return state
 
@@ -599,6 +625,7 @@ class Engine:
             g = self.comm.all_gather(pad)  # [W, ncols, Mmax]
             pend["gathered"] = torch.cuda.Event()
             pend["gathered"].record(torch.cuda.current_stream())
+            self._mark("sample_gathered")
             # ranks whose chunks could not supply their share contribute what they have; the
             # order statistics below are taken over the slots every rank agreed on (host arithmetic)
             sample = torch.cat([g[r, :, : M_ranks[r]] for r in range(self.comm.world)], dim=1).contiguous()
@@ -711,17 +738,41 @@ class Engine:
         else:  # overflow of any rank's buffer is encoded as a count above _NO_CAP
             nat.call("txf_qresolve", pend["cells"].data_ptr(), pend["edges"].data_ptr(), global_count.data_ptr(), _NO_CAP,
                      ranks_dev.data_ptr(), ncols, T, direct.data_ptr(), cand_rank.data_ptr(), status.data_ptr(), s)
-        cptrs = nat.ptr_array([cand[c].data_ptr() for c in range(ncols)])
+        pend.update(status=status, direct=direct, cand_rank=cand_rank, reduce=global_count is not None)
+        self._quantiles_select(nb, pend, use_bracket_hist=self.bracket_select)
 
-        def cand_pass(st, p):
-            nat.call("txf_msel_hist", st, ncols, T, p, cptrs, None, None, 1, cand.shape[1], cand_count.data_ptr(), s)
+    def _quantiles_select(self, nb: int, pend, use_bracket_hist: bool):
+        """The exact order statistic inside every bracket, among the candidates: one histogram pass over the
+        bracket's key range (txf_bsel_*; multi-rank: ONE all-reduce), or -- brackets wider than the histogram,
+        flagged by status bit 4 -- the four-digit radix select (four all-reduces)."""
+        keys, T = pend["keys"], pend["T"]
+        ncols = len(keys)
+        s = self._stream()
+        cand, cand_count, cand_rank, status = pend["cand"], pend["cand_count"], pend["cand_rank"], pend["status"]
+        if use_bracket_hist:
+            B = 16384
+            while B > 256 and 4 * ncols * T * B > (8 << 20):  # keep the histogram (and its all-reduce) under 8 MB
+                B >>= 1
+            hist = self._buf(f"q{nb}_bsel", nat.query("txf_bsel_hist_bytes", ncols, T, B) // 4, torch.int32)
+            nat.call("txf_bsel_hist", cand.data_ptr(), cand.shape[1], cand_count.data_ptr(), pend["edges"].data_ptr(), ncols, T, B,
+                     hist.data_ptr(), s)
+            if pend["reduce"]:
+                self.comm.all_reduce_sum_(hist)
+            sel = self._buf(f"q{nb}_sel_keys", (ncols, T), torch.int32)
+            nat.call("txf_bsel_resolve", hist.data_ptr(), pend["cells"].data_ptr(), pend["edges"].data_ptr(), cand_rank.data_ptr(), ncols, T, B,
+                     sel.data_ptr(), status.data_ptr(), s)
+        else:
+            cptrs = nat.ptr_array([cand[c].data_ptr() for c in range(ncols)])
 
-        sel = self._msel(f"q{nb}_sel", ncols, T, cand_rank, cand_pass, reduce=global_count is not None)
+            def cand_pass(st, p):
+                nat.call("txf_msel_hist", st, ncols, T, p, cptrs, None, None, 1, cand.shape[1], cand_count.data_ptr(), s)
+
+            sel = self._msel(f"q{nb}_sel", ncols, T, cand_rank, cand_pass, reduce=pend["reduce"])
         bounds = self._buf(f"q{nb}_bounds", (ncols, T), torch.float32)
         nbound = self._buf(f"q{nb}_nbound", (ncols,), torch.int32)
-        nat.call("txf_qfinal", direct.data_ptr(), cand_rank.data_ptr(), sel.data_ptr(), ncols, T, bounds.data_ptr(),
+        nat.call("txf_qfinal", pend["direct"].data_ptr(), cand_rank.data_ptr(), sel.data_ptr(), ncols, T, bounds.data_ptr(),
                  nbound.data_ptr(), s)
-        pend.update(status=status, bounds=bounds, nbound=nbound)
+        pend.update(bounds=bounds, nbound=nbound)
 
     @staticmethod
     def _global_cand_count(counts_all: torch.Tensor, caps_all: torch.Tensor) -> torch.Tensor:
@@ -730,7 +781,7 @@ class Engine:
         over = (counts_all > caps_all).any(dim=0)
         return torch.where(over, torch.full_like(counts_all[0], _NO_CAP + 1), counts_all.sum(dim=0)).contiguous()
 
-    def _exchange_fixed(self, pending_q, pending_v, state: Optional[TransformState]):
+    def _exchange_fixed(self, pending_q, pending_v, state: Optional[TransformState], after_moments=None):
         """The exchange step as one collective: every rank packs its vocabulary entries, candidate
         keys and cell counts into a fixed-layout int64 buffer on the device, the buffers are
         all-gathered, and each rank rebuilds the merged state from all rows -- no size ever goes
@@ -774,17 +825,28 @@ class Engine:
             blob[ok:ox].fill_(p["cand_cap"])
             blob[ox:ox + p["cells"].numel()].copy_(p["cells"].flatten())
         g = self.comm.all_gather(blob)  # [W, off] -- the one collective of the exchange
+        self._mark("blob_gathered")
         if nmom:
             o = layout["mom"]
             self._finish_moments(state, g[:, o:o + 3 * nmom].contiguous().view(torch.float64))
         if nmm:
             o = layout["mm"]
             self._finish_minmax(state, g[:, o:o + nmm].contiguous().view(torch.float32))
-        for nb, p in fast:
-            ncols = len(p["keys"])
-            oc, ok, ox = layout[("q", nb)]
-            p["cells"].copy_(g[:, ox:ox + p["cells"].numel()].sum(dim=0).view_as(p["cells"]))
-            self._quantiles_resolve(nb, p, self._global_cand_count(g[:, oc:oc + ncols], g[:, ok:ox]))
+        # The boundary selection is a chain of four small dependent all-reduces (latency, not bytes): it runs on the
+        # quantile stream while this stream merges the vocabularies and -- analyze_and_transform -- already z-scores.
+        main = torch.cuda.current_stream()
+        qs = self._side[0] if (self.overlap_streams and self._side is not None and fast) else main
+        if qs is not main:
+            qs.wait_stream(main)
+        with torch.cuda.stream(qs):
+            for nb, p in fast:
+                ncols = len(p["keys"])
+                oc, ok, ox = layout[("q", nb)]
+                p["cells"].copy_(g[:, ox:ox + p["cells"].numel()].sum(dim=0).view_as(p["cells"]))
+                self._quantiles_resolve(nb, p, self._global_cand_count(g[:, oc:oc + ncols], g[:, ok:ox]))
+            self._mark("boundaries_selected")
+        if after_moments is not None and state is not None:
+            after_moments(state)
         for vk, p in voc:
             cap2 = max(self.vocab_capacity, _pow2_at_least(2 * W * K))
             tag2 = p["tag"] + "_merged"
@@ -794,6 +856,10 @@ class Engine:
             nat.call("txf_vocab_compact", table.data_ptr(), cap2, arena.data_ptr(), ent.data_ptr(), counts_buf.data_ptr(),
                      ctrl.data_ptr(), s)
             p["merged"] = dict(tag=tag2, cap=cap2, table=table, arena=arena, ctrl=ctrl, ent=ent, counts=counts_buf)
+        self._mark("vocab_merged")
+        if qs is not main:
+            main.wait_stream(qs)
+        self._mark("exchange_done")
 
     def _exchange(self, pending_q, pending_v):
         """Sized variant of the exchange (used when a section of the fixed layout overflows, or with
@@ -934,6 +1000,15 @@ class Engine:
                                 torch.zeros((ncols,), dtype=torch.int32, device=self.device), path="empty")
         if pend["fast"] or pend.get("split_done"):
             status = pend["status"].cpu()
+            if pend["fast"] and int(status.max()) == 4 and int((status & ~4).abs().sum()) == 0:
+                # a bracket spans more keys than the one-pass histogram holds (the same verdict on every rank):
+                # select among the candidates by radix digits instead
+                pend["status"] &= ~4
+                self._quantiles_select(nb, pend, use_bracket_hist=False)
+                self.last_quantile_select[nb] = "radix digits"
+                status = pend["status"].cpu()
+            elif pend["fast"]:
+                self.last_quantile_select[nb] = "bracket histogram" if self.bracket_select else "radix digits"
             if int(status.abs().sum()) == 0:
                 path = "sample-select" if pend["fast"] else "splitter-select"
                 self.last_quantile_path[nb] = path
@@ -1285,17 +1360,24 @@ class Engine:
                     xs.wait_event(ev)
                 with torch.cuda.stream(xs):
                     done[:] = [self.transform_state_free(c, o) for c, o in zip(chunks, outs_prev)]
+                    self._mark("stream_kernel_done")
                 for d in done:  # buffers allocated under the side stream are handed to the caller's stream
                     for col in d.values():
                         for t in ((col.values,) if isinstance(col, NumericColumn) else (col.offsets, col.pool)):
                             t.record_stream(main)
 
             self._count_warps = 24
-        def between(state):  # ops that need moments / boundaries only: queued while the vocabularies are still being ranked
+        launched = set()
+
+        def between(state, phase):
+            """Ops whose analyzer results are final are queued while the rest of the state is still being finished:
+            z-scores once the moments are merged (multi-rank: while the boundary selection's all-reduces run),
+            bucket ids once the boundaries are final (while the vocabularies are being ranked)."""
+            kinds = (ZScoreSpec,) if phase == "moments" else (ZScoreSpec, BucketSpec)
+            early = [sp for sp in self.plan.specs if isinstance(sp, kinds) and sp.out_key not in launched]
+            launched.update(sp.out_key for sp in early)
             for i, (c, o) in enumerate(zip(chunks, outs_prev)):
-                early = [sp for sp in self.plan.specs if isinstance(sp, (ZScoreSpec, BucketSpec))]
-                cols = self._run_fused(c, state, o, early, stream_kernel=False)
-                done[i] = dict(done[i] or {}, **cols)
+                done[i] = dict(done[i] or {}, **self._run_fused(c, state, o, early, stream_kernel=False))
 
         try:
             state = self.analyze(chunks, rows_per_rank, side_work if overlap else None, between if overlap else None)
@@ -1304,4 +1386,5 @@ class Engine:
         outs = [self.transform(c, state, o, d) for c, o, d in zip(chunks, outs_prev, done)]
         if overlap:
             torch.cuda.current_stream().wait_stream(xs)
+        self._mark("step_done")
         return (outs[0] if isinstance(data, Table) else outs), state

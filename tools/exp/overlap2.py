@@ -34,6 +34,21 @@ for ov in (True, False):
     ms = loop(ov)
     if rank == 0:
         print(f"world {world} overlap {ov}: {ms:.3f} ms per step", flush=True)
+# event timeline of one overlapped step (TXF_TRACE=1), every rank's view of the slowest points
+if os.environ.get("TXF_TRACE") == "1":
+    eng.overlap_transform = True
+    for _ in range(3):
+        eng.trace_events = []
+        dist.barrier(); torch.cuda.synchronize()
+        o2, _ = eng.analyze_and_transform(t, out, rows_per_rank=rpr)
+        torch.cuda.synchronize()
+        rep = eng.trace_report()
+    allrep = [None] * world
+    dist.all_gather_object(allrep, rep)
+    if rank == 0:
+        for k in rep:
+            vals = [r.get(k, float("nan")) for r in allrep]
+            print(f"trace {k:22s} min {min(vals):7.3f}  max {max(vals):7.3f}", flush=True)
 eng._profile = True
 for _ in range(2):
     eng.timeline.clear()
