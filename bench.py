@@ -76,7 +76,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.gpu}", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits",
-                                          "-lms", "20"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                                          "-lms", "50"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
         except OSError:
@@ -325,7 +325,7 @@ def run_b200(args):
     barrier()
 
     sampler = ClockSampler(local_rank)
-    if rank == 0:
+    if rank == 0 and os.environ.get("TXF_NO_CLOCK_SAMPLER") != "1":
         sampler.start()
     launches0 = nat.launch_count()
     barrier()
@@ -345,6 +345,7 @@ def run_b200(args):
     reps = 3
     a_ms = x_ms = 0.0
     for _ in range(reps):
+        barrier()  # ranks enter each repetition together: otherwise one rank's lateness is booked as the others' analyze time
         ev[0].record()
         st2 = eng.analyze(chunks, rows_per_rank)
         ev[1].record()
@@ -660,13 +661,38 @@ def run_e2e(args, eng, plan, table, out, dev, world, rank, barrier):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item())
 
+    def copies_only(reps):
+        """The same bytes with no compute in between: every input column up, every output column down, both directions at
+        once on all ranks -- the ceiling this box's host links put on the end-to-end step (measured, not assumed)."""
+        o = out_dev[0]
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            with torch.cuda.stream(s_h2d):
+                for k, c in host_in.items():
+                    _copy_col(dev_in[0][k], c)
+            with torch.cuda.stream(s_d2h):
+                for k, c in o.items():
+                    _copy_col_to_host(host_out[k], c)
+        torch.cuda.synchronize()
+        barrier()
+        ms = torch.tensor([(time.perf_counter() - t0) * 1e3 / reps], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
     run(2, True)  # warm-up (allocates every workspace)
     serial_ms = timed(max(args.e2e_steps // 2, 1), False)
     piped_ms = timed(args.e2e_steps, True)
+    copies_only(1)
+    ceiling_ms = copies_only(3)
     return {"value": world * R / (piped_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
             "rows_per_gpu": R, "ms_per_step": piped_ms, "steps": args.e2e_steps, "pipelined": True,
             "serial_ms_per_step": serial_ms, "serial_value": world * R / (serial_ms * 1e-3),
             "copy_gbs_per_gpu_each_way": {"h2d": h2d / (piped_ms * 1e-3) / 1e9, "d2h": d2h / (piped_ms * 1e-3) / 1e9},
+            "pcie_ceiling": {"ms_per_step": ceiling_ms, "gbs_per_gpu_each_way": max(h2d, d2h) / (ceiling_ms * 1e-3) / 1e9,
+                             "how": "the step's H2D and D2H copies alone, both directions at once on all ranks, 3 repetitions, max over ranks"},
+            "frac_of_ceiling": ceiling_ms / piped_ms,
             "host_numa": _NUMA_NOTE.get("note"),
             "timing": "host wall clock around barrier + synchronize (three streams); max over ranks",
             "api": "Engine.analyze_and_transform on tables copied from pinned host memory; every output column copied back; "

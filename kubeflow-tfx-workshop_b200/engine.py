@@ -416,6 +416,8 @@ class Engine:
             self._analyze_moments(chunks, state, defer)
             self._analyze_minmax(chunks, state, defer)
             self._mark("moments_done")
+            # (one rank: the moments are final here, but z-score tiles queued now would crowd the quantile count pass, which
+            #  is sized as one resident wave -- measured: no gain; they are queued with the bucket ops below instead)
             main.wait_stream(sv)
             main.wait_stream(sq)
             self._mark("local_pass_done")
@@ -426,12 +428,27 @@ class Engine:
             self._analyze_minmax(chunks, state, defer)
             pending_q = {nb: self._quantiles_launch(nb, keys, chunks, n_locals) for nb, keys in self.bucket_groups.items()}
             pending_v = count_vocab()
+        def queue_bucket_ops():
+            """analyze_and_transform: the boundaries of the one- and two-pass engines are selected on the device without any
+            host value, so the ops that need them are queued BEFORE the host waits (no launch gap after the sync).  The
+            status words are read afterwards; a column that has to fall back to the radix select gets its ops queued again."""
+            if between is None or self._profile:
+                return
+            for nb, pend in pending_q.items():
+                if "bounds" in pend:
+                    state.buckets[nb] = BucketResult(list(pend["keys"]), nb, pend["bounds"], pend["nbound"], path="pending")
+            if len(state.buckets) == len(pending_q):
+                between(state, "boundaries")
+
         if self.comm.active and self.fixed_exchange and not self._profile:
             # the fixed-layout exchange needs no value from the host: queue it behind the local pass
             # so that its launches are issued while the GPU is still busy, then wait once
             self._exchange_fixed(pending_q, pending_v, state, (lambda st: between(st, "moments")) if between is not None else None)
+            queue_bucket_ops()
             main.synchronize()
         else:
+            if not self.comm.active:
+                queue_bucket_ops()
             # one host round trip: everything queued above has to finish before sizes/flags are read
             main.synchronize()
             self._tick("local_pass")
@@ -443,6 +460,8 @@ class Engine:
                 self._tick("exchange")
         for nb, pend in pending_q.items():
             state.buckets[nb] = self._quantiles_finish(nb, pend, chunks, n_total)
+            if between is not None and (state.buckets[nb].path == "radix-select" or pend.get("recomputed")) and not self._profile:
+                between(state, "boundaries-again")  # the optimistic launch above used boundaries that were not final
         self._tick("quantiles_finish")
         rank_stream = main
         if between is not None and self.overlap_streams and pending_v:
@@ -1004,6 +1023,7 @@ class Engine:
                 # a bracket spans more keys than the one-pass histogram holds (the same verdict on every rank):
                 # select among the candidates by radix digits instead
                 pend["status"] &= ~4
+                pend["recomputed"] = True
                 self._quantiles_select(nb, pend, use_bracket_hist=False)
                 self.last_quantile_select[nb] = "radix digits"
                 status = pend["status"].cpu()
@@ -1353,6 +1373,12 @@ class Engine:
             if self._xstream is None:
                 self._xstream = torch.cuda.Stream(device=self.device)
             xs = self._xstream
+            # A timing event on the caller's stream at the start of every step.  Measured, not explained: when the CUDA context
+            # was created with the default 8 host->device work queues (i.e. before this package could set
+            # CUDA_DEVICE_MAX_CONNECTIONS), back-to-back steps serialise part of the four streams' work (7.55 ms per step);
+            # with this record they do not (6.57 ms), the same as with 32 queues (tools/exp/conn.py).
+            self._step_mark = torch.cuda.Event(enable_timing=True)
+            self._step_mark.record(main)
             xs.wait_stream(main)
 
             def side_work(events):  # called by analyze at the point where the stream kernel may start (see _analyze_once)
@@ -1374,6 +1400,8 @@ class Engine:
             z-scores once the moments are merged (multi-rank: while the boundary selection's all-reduces run),
             bucket ids once the boundaries are final (while the vocabularies are being ranked)."""
             kinds = (ZScoreSpec,) if phase == "moments" else (ZScoreSpec, BucketSpec)
+            if phase == "boundaries-again":
+                launched.difference_update(sp.out_key for sp in self.plan.specs if isinstance(sp, BucketSpec))
             early = [sp for sp in self.plan.specs if isinstance(sp, kinds) and sp.out_key not in launched]
             launched.update(sp.out_key for sp in early)
             for i, (c, o) in enumerate(zip(chunks, outs_prev)):
