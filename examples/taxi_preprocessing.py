@@ -1,7 +1,7 @@
 """A preprocessing_fn for the Chicago-taxi features, written against the tf / tft API exactly as a
 TFX user would (same feature groups, same tft calls and arguments as the reference pipeline's
 ``airflow-dags/taxi_utils.py:86-145``).  The GPU box has no /root/reference, so the GPU tests and
-the benchmark trace this module; ``tests/test_shims.py`` checks, where the reference file is
+the benchmark trace this module; ``tests/test_host.py::test_reference_taxi_utils_runs_unmodified_through_the_shims`` checks, where the reference file is
 present, that both trace to the same plan.
 
 Import it under ``kubeflow_tfx_workshop_b200.install_shims()`` (or with real TF/tft installed).

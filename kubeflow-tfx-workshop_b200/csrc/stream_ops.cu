@@ -16,8 +16,6 @@
 //
 // Algorithmic bytes: every input cell read once, every output cell written once (SURVEY.md 8d:
 // 56 + 4 + 8 B read and 56 + 4 B written per row on the taxi schema for these ops).
-#include <cstdlib>
-
 #include "common.cuh"
 #include "str_pipe.cuh"
 
@@ -325,11 +323,7 @@ int txf_transform_stream(const txf_op* ops, int nops, int64_t n, void* workspace
   // analyzer CTA that needs 185 KB could not join this kernel's CTA on the SM before it has finished
   TXF_CUDA(cudaFuncSetAttribute(stream_ops_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
   const long long want = (jobs + kSsChunk - 1) / kSsChunk;
-  int grid = static_cast<int>(want < kSMs ? want : kSMs);
-  if (const char* e = getenv("TXF_PERSISTENT_CTAS")) {  // experiment knob: leave some SMs free of the persistent kernels
-    const int lim = atoi(e);
-    if (lim >= 1 && lim < grid) grid = lim;
-  }
+  const int grid = static_cast<int>(want < kSMs ? want : kSMs);
   stream_ops_kernel<<<grid, kSsThreads, kSsSmemBytes, cs>>>(prog, static_cast<unsigned long long*>(workspace_dev));
   TXF_LAUNCH_CHECK();
   count_launch(1);

@@ -18,8 +18,6 @@
 // Ranking reproduces tft: drop '' and terms containing \n / \r, order by (count, bytes)
 // descending, keep top_k.
 // Algorithmic bytes of the count pass: 4 (offset) + term bytes per row + 1 validity bit.
-#include <cstdlib>
-
 #include "vocab.cuh"
 #include "str_pipe.cuh"
 
@@ -216,8 +214,8 @@ struct VcSource {
 };
 
 // lane 0 of the owning warp: start the copies of step rows [r0, r1) into the stage
-__device__ __forceinline__ void vc_issue(const VcSource& src, const VcStage& st, uint64_t* bar, uint32_t r0, uint32_t r1) {
-  const uint32_t b0 = static_cast<uint32_t>(__ldg(src.offsets + r0)), e0 = static_cast<uint32_t>(__ldg(src.offsets + r1));
+__device__ __forceinline__ void vc_issue(const VcSource& src, const VcStage& st, uint64_t* bar, uint32_t r0, uint32_t r1, uint32_t b0,
+                                         uint32_t e0) {  // b0, e0 = offsets[r0], offsets[r1] (loaded by the caller well ahead of this call)
   const uint32_t start = b0 & ~15u;
   const uint32_t need = ((e0 - start + 15u) & ~15u) + 32u;  // window loads touch < 24 bytes past a term
   const bool do_bytes = src.pool_ok && need <= static_cast<uint32_t>(kVcStageCap);
@@ -338,15 +336,23 @@ __global__ void __launch_bounds__(kVcWarps * 32, 1) __maxnreg__(kVcWarps == kVcW
   const uint32_t nsteps = (n32 + kVcStepRows - 1) / kVcStepRows;
   const uint32_t gw = blockIdx.x * kVcWarps + warp, nw = gridDim.x * kVcWarps;
   auto step_end = [&](uint32_t t) { return (t + 1) * kVcStepRows < n32 ? (t + 1) * kVcStepRows : n32; };
+  auto off_at = [&](uint32_t row) { return static_cast<uint32_t>(__ldg(offsets + row)); };
   if (lane_id() == 0) {
-    if (gw < nsteps) vc_issue(src, VcStage{wbase}, &bars[0], gw * kVcStepRows, step_end(gw));
-    if (gw + nw < nsteps) vc_issue(src, VcStage{wbase + kVcStageBytes}, &bars[1], (gw + nw) * kVcStepRows, step_end(gw + nw));
+    if (gw < nsteps) vc_issue(src, VcStage{wbase}, &bars[0], gw * kVcStepRows, step_end(gw), off_at(gw * kVcStepRows), off_at(step_end(gw)));
+    if (gw + nw < nsteps)
+      vc_issue(src, VcStage{wbase + kVcStageBytes}, &bars[1], (gw + nw) * kVcStepRows, step_end(gw + nw), off_at((gw + nw) * kVcStepRows),
+               off_at(step_end(gw + nw)));
   }
   uint32_t k = 0;
   int empty_slot = -1;  // front-table slot of the empty term once this warp has met it (warp-uniform)
   for (uint32_t t = gw; t < nsteps; t += nw, ++k) {
     const int s = k & 1;
     const uint32_t r0 = t * kVcStepRows, r1 = step_end(t);
+    // the refill of this stage (issued after the step) needs two offsets from global memory: lane 0 asks for them now,
+    // a whole step ahead of their use, so that the warp does not sit out two dependent global-load latencies per step
+    const uint32_t nxt = t + 2 * nw;
+    uint32_t nb0 = 0, ne0 = 0;
+    if (lane_id() == 0 && nxt < nsteps) { nb0 = off_at(nxt * kVcStepRows); ne0 = off_at(step_end(nxt)); }
     mbar_wait(&bars[s], (k >> 1) & 1u);
     const VcStage st{wbase + s * kVcStageBytes};
     // two instantiations only (the kernel is issue-bound and its code must stay in the instruction cache): the
@@ -355,8 +361,7 @@ __global__ void __launch_bounds__(kVcWarps * 32, 1) __maxnreg__(kVcWarps == kVcW
     if (st.staged() && st.meta()) vc_step<true, true>(f, src, st, r0, r1, wqueue, s_mask, empty_slot, front_long);
     else vc_step<false, false>(f, src, st, r0, r1, wqueue, s_mask, empty_slot, front_long);
     __syncwarp();  // every lane is done with the stage: refill it with the step after next
-    const uint32_t nxt = t + 2 * nw;
-    if (lane_id() == 0 && nxt < nsteps) vc_issue(src, st, &bars[s], nxt * kVcStepRows, step_end(nxt));
+    if (lane_id() == 0 && nxt < nsteps) vc_issue(src, st, &bars[s], nxt * kVcStepRows, step_end(nxt), nb0, ne0);
   }
   __syncthreads();
   for (int i = threadIdx.x; i < kVcSlots; i += kVcBlock) {  // flush the front table
@@ -676,10 +681,6 @@ int txf_vocab_count(const int32_t* offsets_dev, const uint8_t* pool_dev, const u
   const int warps = cta_warps == 0 ? kVcWarpsFull : cta_warps;
   int64_t want = (n + static_cast<int64_t>(kVcStepRows) * warps - 1) / (static_cast<int64_t>(kVcStepRows) * warps);
   int grid = static_cast<int>(want < kVcGrid ? want : kVcGrid);
-  if (const char* e = getenv("TXF_PERSISTENT_CTAS")) {  // experiment knob: leave some SMs free of the persistent kernels
-    const int lim = atoi(e);
-    if (lim >= 1 && lim < grid) grid = lim;
-  }
   auto launch = [&](auto kernel, int w) -> int {
     TXF_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(vc_smem_bytes(w))));
     TXF_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));

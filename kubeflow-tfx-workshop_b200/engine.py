@@ -395,9 +395,8 @@ class Engine:
         if self.overlap_streams:
             with torch.cuda.stream(sq):
                 pending_q = {nb: self._quantiles_sample(nb, keys, chunks, n_locals) for nb, keys in self.bucket_groups.items()}
-            wait_gather = os.environ.get("TXF_NO_GATHER_WAIT") != "1"  # experiment knob
             if side_work is not None:
-                side_work([pq["gathered"] for pq in pending_q.values() if pq.get("gathered") is not None] if wait_gather else [])
+                side_work([pq["gathered"] for pq in pending_q.values() if pq.get("gathered") is not None])
                 side_work = None
             if pending_v is None:
                 # Row counts came from the caller, so nothing made the host wait above.  The count pass is queued right BEHIND
@@ -405,7 +404,7 @@ class Engine:
                 # millisecond to enqueue): a collective kernel cannot become resident once the persistent count CTAs (plus the
                 # stream kernel) hold every SM's registers, and the quantile pass would wait for the whole count pass.
                 for pq in pending_q.values():
-                    if pq.get("gathered") is not None and wait_gather:
+                    if pq.get("gathered") is not None:
                         sv.wait_event(pq["gathered"])
                 with torch.cuda.stream(sv):
                     pending_v = count_vocab()
