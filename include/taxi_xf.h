@@ -378,6 +378,52 @@ TXF_API int txf_example_encode(const txf_example_feature* feats, int nfeat, cons
                                const int64_t* offsets_dev, uint8_t* out_dev, txf_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------
+ * TFRecord / tf.Example DECODE on the GPU (ingest): what a TFX Transform executor is fed
+ * (airflow-dags/taxi_pipeline.py:70-89; the reader is named at airflow-dags/taxi_utils.py:79-83 and used at
+ * :260-281).  data_dev: the UNCOMPRESSED record stream (gunzip stays on the host), 16-byte aligned, with at
+ * least 16 readable bytes past nbytes; nbytes < 2^31.
+ *   1. txf_tfrecord_count_candidates -> block_counts_dev[ceil(nbytes / txf_tfrecord_block_bytes())]: positions
+ *      that look like a record start (length field < 2^31 whose masked CRC-32C matches)
+ *   2. caller: exclusive prefix sum -> block_base_dev (int64); ncand = sum
+ *   3. txf_tfrecord_candidates -> cand_dev[ncand], ascending
+ *   4. txf_tfrecord_link -> mark_dev[ncand]: 1 for position 0 and for every candidate some candidate's record
+ *      ends at.  The marked candidates, in order, are the records; the caller checks that each one ends where
+ *      the next begins and the last one at nbytes (anything else is a corrupt file) and appends nbytes:
+ *      record_start_dev[n + 1]
+ *   5. txf_example_decode: row i of every requested feature from record i.  A feature that is absent or has
+ *      an empty list is a missing cell (validity 0, value 0 / length 0); one value is the cell; more than one
+ *      sets TXF_EX_ERR_MULTI (the reference requires at most one value per row, taxi_utils.py:92-93).
+ *      status_dev[0] = OR of TXF_EX_ERR_*, status_dev[1] = smallest offending record (caller: 0, UINT64_MAX)
+ *   6. per string feature: caller prefix-sums lens into int32 offsets, then txf_gather_bytes
+ * ------------------------------------------------------------------------------------------ */
+enum {
+  TXF_EX_ERR_TRUNCATED = 1, /* the length field does not match the record's extent */
+  TXF_EX_ERR_WIRE = 2,      /* malformed protobuf wire data */
+  TXF_EX_ERR_KIND = 4,      /* a feature holds a list of another kind than requested */
+  TXF_EX_ERR_MULTI = 8,     /* more than one value in a cell */
+  TXF_EX_ERR_CRC = 16       /* data CRC mismatch (verify_crc) */
+};
+typedef struct txf_example_column {
+  int32_t kind;     /* TXF_F32 | TXF_I64 | TXF_EX_BYTES */
+  int32_t name_off;
+  int32_t name_len;
+  int32_t reserved;
+  void* values;     /* float[n] | int64[n] | uint32 position of the bytes in the stream[n] (strings) */
+  int32_t* lens;    /* strings: byte length[n]; else NULL */
+  void* valid;      /* bitmap, ceil(n / 32) * 4 bytes, 4-byte aligned */
+} txf_example_column;
+TXF_API int64_t txf_tfrecord_block_bytes(void);
+TXF_API int txf_tfrecord_count_candidates(const uint8_t* data_dev, int64_t nbytes, uint32_t* block_counts_dev, txf_stream_t stream);
+TXF_API int txf_tfrecord_candidates(const uint8_t* data_dev, int64_t nbytes, const int64_t* block_base_dev, int64_t* cand_dev,
+                                    txf_stream_t stream);
+TXF_API int txf_tfrecord_link(const uint8_t* data_dev, const int64_t* cand_dev, int64_t ncand, uint8_t* mark_dev, txf_stream_t stream);
+TXF_API int txf_example_decode(const txf_example_column* feats, int nfeat, const uint8_t* names_dev, const uint8_t* data_dev,
+                               const int64_t* record_start_dev, int64_t n, int verify_crc, uint64_t* status_dev,
+                               txf_stream_t stream);
+TXF_API int txf_gather_bytes(const uint8_t* data_dev, const uint32_t* pos_dev, const int32_t* offsets_dev, int64_t n,
+                             uint8_t* pool_dev, txf_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
  * Sibling analyzers / mappers of the workshop notebooks.
  *   min/max analyzer + tft.scale_to_0_1 / scale_by_min_max:
  *     notebooks/03_TensorFlow_Transform.ipynb:148, 03a_TensorFlow_Transform_Advanced.ipynb:323,333

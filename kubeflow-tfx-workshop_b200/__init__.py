@@ -33,7 +33,7 @@ from .columns import NumericColumn, StringColumn, Table
 from .dist import Comm, shard_range
 from .engine import Engine, TransformState
 from .egress import encode_tfrecord, write_tfrecord
-from .ingest import read_csv
+from .ingest import read_csv, read_tfrecord
 from .plan import Plan, trace
 from .state import TFTransformOutput, load_state, save_state
 
@@ -41,7 +41,7 @@ tf = tf_shim
 tft = tft_shim
 
 __all__ = ["Table", "NumericColumn", "StringColumn", "Engine", "TransformState", "Plan", "trace", "Comm", "shard_range",
-           "tf", "tft", "tft_beam", "tf_metadata", "save_state", "load_state", "TFTransformOutput", "read_csv", "encode_tfrecord", "write_tfrecord", "install_shims"]
+           "tf", "tft", "tft_beam", "tf_metadata", "save_state", "load_state", "TFTransformOutput", "read_csv", "read_tfrecord", "encode_tfrecord", "write_tfrecord", "install_shims"]
 
 _SHIM_MODULES = {
     "tensorflow": tf_shim,

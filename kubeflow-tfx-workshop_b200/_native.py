@@ -55,6 +55,16 @@ class TxfExampleFeature(Structure):
                 ("values", c_void_p), ("pool", c_void_p), ("valid", c_void_p)]
 
 
+class TxfExampleColumn(Structure):
+    """struct txf_example_column (include/taxi_xf.h)."""
+
+    _fields_ = [("kind", c_int32), ("name_off", c_int32), ("name_len", c_int32), ("reserved", c_int32),
+                ("values", c_void_p), ("lens", c_void_p), ("valid", c_void_p)]
+
+
+EX_ERRORS = {1: "a record's length field does not match its extent", 2: "malformed protobuf wire data",
+             4: "a feature holds a list of another kind than the schema says", 8: "more than one value in a cell",
+             16: "data CRC mismatch"}
 TXF_EX_BYTES = 2
 TXF_EX_MAX_FEATURES = 64
 ARITH_ADD, ARITH_SUB, ARITH_MUL, ARITH_DIV = range(4)
@@ -140,6 +150,12 @@ _SIGNATURES = {
     "txf_csv_copy_strings": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
     "txf_example_sizes": (c_int, [POINTER(TxfExampleFeature), c_int, c_int64, c_void_p, c_void_p]),
     "txf_example_encode": (c_int, [POINTER(TxfExampleFeature), c_int, c_void_p, c_int64, c_void_p, c_void_p, c_void_p]),
+    "txf_tfrecord_block_bytes": (c_int64, []),
+    "txf_tfrecord_count_candidates": (c_int, [c_void_p, c_int64, c_void_p, c_void_p]),
+    "txf_tfrecord_candidates": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p]),
+    "txf_tfrecord_link": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
+    "txf_example_decode": (c_int, [POINTER(TxfExampleColumn), c_int, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p, c_void_p]),
+    "txf_gather_bytes": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
     "txf_fingerprint64_batch": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
 }
 

@@ -15,7 +15,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 INCLUDE = os.path.join(HERE, "..", "include")
 LIB = os.path.join(HERE, "libtaxi_xf.so")
-SOURCES = ["api.cu", "moments.cu", "quantile.cu", "vocab.cu", "transform.cu", "stream_ops.cu", "siblings.cu", "csv.cu", "example.cu"]
+SOURCES = ["api.cu", "moments.cu", "quantile.cu", "vocab.cu", "transform.cu", "stream_ops.cu", "siblings.cu", "csv.cu", "example.cu", "example_decode.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
     "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden", "--expt-relaxed-constexpr",

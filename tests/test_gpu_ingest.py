@@ -187,3 +187,134 @@ def test_fuzz_small_files_against_csv_module(ktw):
         table = ktw.read_csv(data, schema=kinds)
         assert len(table) == nrows, (trial, text)
         check_table(table, python_parse(data, kinds))
+
+
+# ------------------------------------------------------------------------------------------------
+# TFRecord / tf.Example decode on the GPU (csrc/example_decode.cu, ingest.read_tfrecord)
+# ------------------------------------------------------------------------------------------------
+def _assert_tables_equal(got, want_cols):
+    for k, c in want_cols.items():
+        g = got[k]
+        if isinstance(c, O.StrCol):
+            assert g.to_list() == c.to_list(), k
+            off, pool, valid = g.numpy()
+            assert np.array_equal(valid, c.valid), k
+        else:
+            v, valid = g.numpy()
+            assert v.dtype == c.values.dtype and np.array_equal(valid, c.valid), k
+            a, b = np.where(valid, v, 0), np.where(c.valid, c.values, 0)
+            assert np.array_equal(a.view(np.uint32) if a.dtype == np.float32 else a, b.view(np.uint32) if b.dtype == np.float32 else b), k
+
+
+def _example_cols(n, rng):
+    words = [b"", b"Cash", b"Credit Card", bytes(range(256)), b"x" * 300, "ünï".encode(), b"\x0a\x12\x1a"]
+    ints = rng.integers(-2 ** 63, 2 ** 63 - 1, n, dtype=np.int64)
+    ints[: min(n, 8)] = np.array([0, 1, -1, 127, 128, 2 ** 63 - 1, -2 ** 63, 300])[: min(n, 8)]
+    floats = rng.standard_normal(n).astype(np.float32)
+    floats[: min(n, 4)] = np.array([np.inf, -0.0, 1e-45, 3.4e38], np.float32)[: min(n, 4)]
+    text = [words[i] for i in rng.integers(0, len(words), n)]
+    keep = rng.random(n) > 0.15
+    return {
+        "zeta": O.NumCol(floats, rng.random(n) > 0.2),
+        "alpha_int": O.NumCol(ints, rng.random(n) > 0.1),
+        "text": O.StrCol.from_list([w if k else None for w, k in zip(text, keep)]),
+        "small": O.NumCol(rng.integers(0, 1010, n).astype(np.int64), None),
+        "a-very-long-feature-name-" + "n" * 120: O.NumCol(rng.integers(0, 10, n).astype(np.int64), None),
+    }
+
+
+@pytest.mark.parametrize("n", [1, 2, 31, 32, 33, 127, 128, 129, 3001, 50_000])
+def test_tfrecord_decode_round_trip(ktw, n):
+    """Records produced by the GPU encoder (byte-identical to protobuf's, tests/test_gpu_egress.py) decode back
+    to the same columns: values, validity (an empty value list is a missing cell), string bytes."""
+    rng = np.random.default_rng(n)
+    cols = _example_cols(n, rng)
+    # a present-but-empty string is written as a one-value list holding b"": it must come back present
+    table = helpers.table_from_oracle(cols, ktw).to("cuda")
+    data, _ = ktw.encode_tfrecord(table)
+    schema = {k: ("bytes" if isinstance(c, O.StrCol) else "float32" if c.values.dtype == np.float32 else "int64") for k, c in cols.items()}
+    got = ktw.read_tfrecord(data, schema)
+    assert len(got) == n
+    _assert_tables_equal(got, cols)
+    # a subset of the features, in another order; a feature no record has is all-missing
+    sub = {"text": "bytes", "never_there": "int64", "zeta": "float32"}
+    got2 = ktw.read_tfrecord(data.cpu().numpy().tobytes(), sub)
+    _assert_tables_equal(got2, {"text": cols["text"], "zeta": cols["zeta"]})
+    assert got2["never_there"].numpy()[1].sum() == 0
+
+
+def test_tfrecord_decode_of_protobuf_runtime_bytes_gzip_and_unpacked_lists(ktw, tmp_path):
+    """Records written by the protobuf runtime (the oracle's encoder), through a gzip file like the reference's;
+    plus hand-built Examples with UNPACKED repeated fields, unknown features, unknown fields and the map entries
+    in reverse order -- all legal wire forms of the same message."""
+    sys_path = helpers.ROOT
+    import sys
+    sys.path.insert(0, sys_path)
+    from oracle import example_oracle as E
+    import gzip
+    rng = np.random.default_rng(9)
+    n = 777
+    cols = _example_cols(n, rng)
+    per = {}
+    for k, c in cols.items():
+        if isinstance(c, O.StrCol):
+            per[k] = ("bytes", c.to_list(), c.valid)
+        else:
+            per[k] = ("float32" if c.values.dtype == np.float32 else "int64", c.values.tolist(), c.valid)
+    rows = [{k: (kind, vals[i] if valid[i] else None) for k, (kind, vals, valid) in per.items()} for i in range(n)]
+    path = tmp_path / "part-00000.gz"
+    with gzip.open(path, "wb") as f:
+        f.write(E.encode_rows(rows))
+    schema = {k: v[0] for k, v in per.items()}
+    _assert_tables_equal(ktw.read_tfrecord(str(path), schema), cols)
+
+    def varint(v):
+        out = b""
+        v &= (1 << 64) - 1
+        while v >= 0x80:
+            out += bytes([(v & 0x7F) | 0x80]); v >>= 7
+        return out + bytes([v])
+
+    def ld(tag, payload):  # length-delimited field
+        return bytes([tag]) + varint(len(payload)) + payload
+
+    def example(entries):
+        feats = b"".join(ld(0x0A, ld(0x0A, k) + ld(0x12, feat)) for k, feat in entries)
+        return ld(0x0A, feats)
+
+    f_unpacked = ld(0x12, bytes([0x0D]) + np.float32(2.5).tobytes())                 # FloatList, value as fixed32 field
+    i_unpacked = ld(0x1A, bytes([0x08]) + varint(-7))                                  # Int64List, value as varint field
+    b_val = ld(0x0A, ld(0x0A, b"hello"))
+    recs = [
+        example([(b"s", b_val), (b"i", i_unpacked), (b"f", f_unpacked)]),              # reverse name order, unpacked
+        example([(b"unknown", ld(0x1A, ld(0x0A, varint(5)))), (b"f", ld(0x12, b""))]) + bytes([0x18, 0x05]),  # unknown feature / field, empty list
+        example([(b"i", ld(0x1A, ld(0x0A, varint(2 ** 63 - 1))))]),
+        b"",                                                                            # an empty Example
+    ]
+    stream = b"".join(E.frame(r) for r in recs)
+    got = ktw.read_tfrecord(stream, {"f": "float32", "i": "int64", "s": "bytes"})
+    assert got["f"].numpy()[0].tolist() == [2.5, 0.0, 0.0, 0.0] and got["f"].numpy()[1].tolist() == [True, False, False, False]
+    assert got["i"].numpy()[0].tolist() == [-7, 0, 2 ** 63 - 1, 0] and got["i"].numpy()[1].tolist() == [True, False, True, False]
+    assert got["s"].to_list() == [b"hello", b"", b"", b""]
+
+
+def test_tfrecord_decode_errors(ktw):
+    import sys
+    sys.path.insert(0, helpers.ROOT)
+    from oracle import example_oracle as E
+    good = E.encode_rows([{"a": ("int64", 1)}, {"a": ("int64", 2)}, {"a": ("int64", 3)}])
+    assert ktw.read_tfrecord(good, {"a": "int64"})["a"].numpy()[0].tolist() == [1, 2, 3]
+    bad = bytearray(good)
+    bad[14] ^= 0x40                                       # payload byte of record 0: data CRC mismatch
+    with pytest.raises(ktw._native.NativeError, match="record 0.*CRC"):
+        ktw.read_tfrecord(bytes(bad), {"a": "int64"})
+    bad = bytearray(good)
+    bad[len(good) // 3 + 2] ^= 0xFF                       # inside the second record's header: the chain breaks there
+    with pytest.raises(ktw._native.NativeError, match="corrupt|does not start"):
+        ktw.read_tfrecord(bytes(bad), {"a": "int64"})
+    two = E.frame(bytes([0x0A, 0x0D, 0x0A, 0x0B, 0x0A, 0x01, 0x61, 0x12, 0x06, 0x1A, 0x04, 0x0A, 0x02, 0x01, 0x02]))  # a: Int64List [1, 2]
+    with pytest.raises(ktw._native.NativeError, match="more than one value"):
+        ktw.read_tfrecord(two, {"a": "int64"})
+    with pytest.raises(ktw._native.NativeError, match="another kind"):
+        ktw.read_tfrecord(good, {"a": "float32"})
+    assert len(ktw.read_tfrecord(b"", {"a": "int64"})) == 0

@@ -63,6 +63,13 @@ def main():
     ms_enc = timed(lambda: ktw.encode_tfrecord(sub))
     enc_bytes = int(ktw.encode_tfrecord(sub)[1][-1].item())
 
+    # decode of those records back into columns (record index + protobuf parse on the device)
+    enc_data = ktw.encode_tfrecord(sub)[0]
+    dec_schema = sub.schema()
+    assert len(ktw.read_tfrecord(enc_data, dec_schema)) == len(sub)
+    ms_dec = timed(lambda: ktw.read_tfrecord(enc_data, dec_schema))
+    ms_dec_nocrc = timed(lambda: ktw.read_tfrecord(enc_data, dec_schema, verify_crc=False))
+
     import pyarrow.csv as pacsv
     t0 = time.perf_counter()
     pacsv.read_csv(io.BytesIO(text))
@@ -84,6 +91,8 @@ def main():
         "gpu_e2e_from_pinned_host": {"ms": ms_e2e, "GBps_text": nbytes / ms_e2e / 1e6, "rows_per_s": nrows / ms_e2e * 1e3},
         "gpu_tfrecord_encode": {"rows": len(sub), "features": len(list(sub.keys())), "ms": ms_enc, "out_mb": enc_bytes / 1e6,
                                 "rows_per_s": len(sub) / ms_enc * 1e3, "GBps_out": enc_bytes / ms_enc / 1e6},
+        "gpu_tfrecord_decode": {"rows": len(sub), "features": len(list(sub.keys())), "in_mb": enc_bytes / 1e6, "ms": ms_dec,
+                                "rows_per_s": len(sub) / ms_dec * 1e3, "GBps_in": enc_bytes / ms_dec / 1e6, "ms_without_data_crc": ms_dec_nocrc},
         "pyarrow_host": {"s": t_arrow, "GBps_text": nbytes / t_arrow / 1e9, "rows_per_s": nrows / t_arrow, "threads": os.cpu_count()},
         "python_row_loop": {"rows": sample_rows, "s": t_py, "rows_per_s": sample_rows / t_py, "threads": 1},
     }))
