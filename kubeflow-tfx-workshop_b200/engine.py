@@ -439,17 +439,29 @@ class Engine:
             if len(state.buckets) == len(pending_q):
                 between(state, "boundaries")
 
+        # The host waits for the analyzer state (an event), NOT for the ops queued behind it: the finishing work below reads a
+        # few control words and launches a dozen tiny kernels, on a side stream, while the main stream already transforms.
+        fin = self._side[1] if (between is not None and self.overlap_streams and not self._profile) else main
+        state_ready = torch.cuda.Event()
+
+        def wait_for_state():
+            state_ready.record(main)
+            queue_bucket_ops()
+            if fin is not main:
+                fin.wait_event(state_ready)
+            state_ready.synchronize()
+
         if self.comm.active and self.fixed_exchange and not self._profile:
             # the fixed-layout exchange needs no value from the host: queue it behind the local pass
             # so that its launches are issued while the GPU is still busy, then wait once
             self._exchange_fixed(pending_q, pending_v, state, (lambda st: between(st, "moments")) if between is not None else None)
-            queue_bucket_ops()
-            main.synchronize()
+            wait_for_state()
         else:
             if not self.comm.active:
-                queue_bucket_ops()
+                wait_for_state()
+            else:
+                main.synchronize()
             # one host round trip: everything queued above has to finish before sizes/flags are read
-            main.synchronize()
             self._tick("local_pass")
             if self.comm.active:
                 if self.fixed_exchange:
@@ -457,24 +469,29 @@ class Engine:
                 else:
                     self._exchange(pending_q, pending_v)
                 self._tick("exchange")
-        for nb, pend in pending_q.items():
-            state.buckets[nb] = self._quantiles_finish(nb, pend, chunks, n_total)
-            if between is not None and (state.buckets[nb].path == "radix-select" or pend.get("recomputed")) and not self._profile:
-                between(state, "boundaries-again")  # the optimistic launch above used boundaries that were not final
+                if fin is not main:
+                    fin.wait_stream(main)
+        redo_buckets = False
+        with torch.cuda.stream(fin):
+            for nb, pend in pending_q.items():
+                state.buckets[nb] = self._quantiles_finish(nb, pend, chunks, n_total)
+                redo_buckets |= state.buckets[nb].path == "radix-select" or bool(pend.get("recomputed"))
+        if fin is not main:
+            if redo_buckets or any("bounds" not in p for p in pending_q.values()):
+                main.wait_stream(fin)  # boundaries were (re)computed on the side stream
+            if between is not None:
+                # first launch (general engine) or again (the optimistic launch used boundaries that were not final)
+                between(state, "boundaries-again" if redo_buckets else "boundaries")
         self._tick("quantiles_finish")
-        rank_stream = main
-        if between is not None and self.overlap_streams and pending_v:
-            between(state, "boundaries")
-            rank_stream = self._side[1]  # everything queued so far has completed (host sync above): no event needed to start
-        with torch.cuda.stream(rank_stream):
+        with torch.cuda.stream(fin):
             for vk, pend in pending_v.items():
                 state.vocabs[vk] = self._vocab_finish(vk, self.vocab_specs[vk], pend)
                 for spec in self.plan.of(VocabSpec):  # decode tables depend on num_oov_buckets / default_value
                     if _vocab_key(spec) == vk:
                         self._decode_tables(vk, spec, pend, state.vocabs[vk], state)
                         break
-        if rank_stream is not main:
-            main.wait_stream(rank_stream)
+        if fin is not main:
+            main.wait_stream(fin)
         self._mark("analyze_done")
         self._tick("vocab_finish")
         return state
