@@ -284,8 +284,8 @@ class Engine:
         """ms from the first mark to every later one (call after a device synchronize)."""
         if not self.trace_events:
             return {}
-        t0 = self.trace_events[0][1]
-        out = {name: round(t0.elapsed_time(ev), 3) for name, ev in self.trace_events[1:]}
+        t0 = next((ev for name, ev in self.trace_events if name == "analyze_start"), self.trace_events[0][1])
+        out = {name: round(t0.elapsed_time(ev), 3) for name, ev in self.trace_events if ev is not t0}
         self.trace_events = []
         return out
 
@@ -369,7 +369,9 @@ class Engine:
         count_vocab = lambda: {vk: self._vocab_count(vk, spec, chunks) for vk, spec in self.vocab_specs.items()}
         if self.overlap_streams:
             if self._side is None:
-                self._side = (torch.cuda.Stream(device=self.device), torch.cuda.Stream(device=self.device))
+                # high priority: their kernels (analyzers, then the short launch-bound finishing chains) are dispatched ahead of
+                # the hundreds of thousands of transform tiles pending on the main stream, instead of after the last of them
+                self._side = (torch.cuda.Stream(device=self.device, priority=-1), torch.cuda.Stream(device=self.device, priority=-1))
             sq, sv = self._side
             start = torch.cuda.Event()
             start.record(main)
@@ -483,6 +485,7 @@ class Engine:
                 # first launch (general engine) or again (the optimistic launch used boundaries that were not final)
                 between(state, "boundaries-again" if redo_buckets else "boundaries")
         self._tick("quantiles_finish")
+        self._mark("early_ops_queued")
         with torch.cuda.stream(fin):
             for vk, pend in pending_v.items():
                 state.vocabs[vk] = self._vocab_finish(vk, self.vocab_specs[vk], pend)
@@ -490,6 +493,7 @@ class Engine:
                     if _vocab_key(spec) == vk:
                         self._decode_tables(vk, spec, pend, state.vocabs[vk], state)
                         break
+            self._mark("vocab_ranked")
         if fin is not main:
             main.wait_stream(fin)
         self._mark("analyze_done")
