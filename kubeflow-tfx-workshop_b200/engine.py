@@ -195,6 +195,10 @@ class Engine:
         self._count_warps = 0        # 24 while analyze_and_transform streams the state-independent ops next to the count pass
         self.overlap_transform = True  # analyze_and_transform: run the ops that need no analyzer result under the analyzers
         self._xstream = None
+        self._step_end = None
+        self.drain_between_steps_world = 4  # see analyze_and_transform
+        self._side_priority = -1          # experiment knobs (tools/exp/ab_wait.py)
+        self._host_waits_on_event = True
         self.sample_size = int(sample_size)
         self.bracket_sigmas = float(bracket_sigmas)
         self.seed = int(seed)
@@ -371,7 +375,7 @@ class Engine:
             if self._side is None:
                 # high priority: their kernels (analyzers, then the short launch-bound finishing chains) are dispatched ahead of
                 # the hundreds of thousands of transform tiles pending on the main stream, instead of after the last of them
-                self._side = (torch.cuda.Stream(device=self.device, priority=-1), torch.cuda.Stream(device=self.device, priority=-1))
+                self._side = tuple(torch.cuda.Stream(device=self.device, priority=self._side_priority) for _ in range(2))
             sq, sv = self._side
             start = torch.cuda.Event()
             start.record(main)
@@ -451,7 +455,10 @@ class Engine:
             queue_bucket_ops()
             if fin is not main:
                 fin.wait_event(state_ready)
-            state_ready.synchronize()
+            if self._host_waits_on_event:
+                state_ready.synchronize()
+            else:
+                main.synchronize()
 
         if self.comm.active and self.fixed_exchange and not self._profile:
             # the fixed-layout exchange needs no value from the host: queue it behind the local pass
@@ -1393,6 +1400,13 @@ class Engine:
             if self._xstream is None:
                 self._xstream = torch.cuda.Stream(device=self.device)
             xs = self._xstream
+            if self.comm.active and self.comm.world >= self.drain_between_steps_world and self._step_end is not None:
+                # 4 and 8 ranks, measured (profiles/r2_ab_wait_4gpu.txt, r2_exchange_timeline_8gpu_head.txt): a step that starts on
+                # an idle GPU takes 6.4-6.7 ms, a step queued while the previous one still runs 7.1-7.6 ms (2 ranks: no such
+                # difference, 6.37 ms queued).  Presumably what a late sample all-gather releases then arrives all at once and
+                # the SMs are taken in priority order, not in the order the pass was laid out in.  So with >= 4 ranks the host
+                # lets the previous step drain first; the launch latency this exposes is part of the 6.4-6.7 ms.
+                self._step_end.synchronize()
             # A timing event on the caller's stream at the start of every step.  Measured, not explained: when the CUDA context
             # was created with the default 8 host->device work queues (i.e. before this package could set
             # CUDA_DEVICE_MAX_CONNECTIONS), back-to-back steps serialise part of the four streams' work (7.55 ms per step);
@@ -1435,4 +1449,7 @@ class Engine:
         if overlap:
             torch.cuda.current_stream().wait_stream(xs)
         self._mark("step_done")
+        if overlap and self.comm.active:
+            self._step_end = torch.cuda.Event()
+            self._step_end.record(torch.cuda.current_stream())
         return (outs[0] if isinstance(data, Table) else outs), state
