@@ -34,6 +34,7 @@ os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 
 METRIC = "preprocessing_fn analyze+transform rows/sec"
 UNIT = "rows/s"
+TAXI_WORKLOAD = "taxi preprocessing_fn analyze+transform on synthetic Chicago-taxi-schema rows "
 ROWS_PER_GPU = 100_000_000  # BASELINE.json configs[1]: 100M synthetic taxi rows on one B200
 CHUNK_ROWS = 100_000_000    # string pools hold < 2^31 bytes: larger shards are lists of chunks
 
@@ -208,7 +209,7 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32/i64/u8", "data": "synthetic",
-        "config": {"workload": "taxi preprocessing_fn analyze+transform, synthetic Chicago-taxi schema", "rows_per_step": rows,
+        "config": {"workload": TAXI_WORKLOAD + "(BASELINE configs[1] per GPU)", "rows_per_step": rows,
                    "note": f"bounded sample ({rows} rows per step) of the 100M-row workload so that the arm ends within minutes; the port's "
                            "time is linear in rows (row-sharded numpy passes + one merge), so rows/s carries over to 100M rows. "
                            "tft/Beam itself is not installable on this box"},
@@ -260,7 +261,7 @@ def _workload(args, ktw, synth, dev, rank, world):
         else:
             lo, hi = rank * args.rows_per_gpu, (rank + 1) * args.rows_per_gpu
         chunks = [synth.taxi_table(min(args.chunk_rows, hi - s), row0=s, backend="torch", device=dev) for s in range(lo, hi, args.chunk_rows)]
-        desc = ("taxi preprocessing_fn analyze+transform on synthetic Chicago-taxi-schema rows "
+        desc = (TAXI_WORKLOAD
                 + ("(BASELINE configs[2]: global rows sharded over the GPUs)" if args.global_rows else "(BASELINE configs[1] per GPU)"))
         return plan, chunks, hi - lo, desc
     mod = _load_example_fn(ktw, "stress_preprocessing")
