@@ -171,7 +171,8 @@ __device__ __forceinline__ void ss_fix_tile(const SsOp& op, long long desc, uint
 // Warp 0 is the producer (lane 0 claims tiles and starts their bulk loads as soon as a stage is free);
 // warps 1..3 are the consumers: they wait for a tile to land, fix it up in place if the op needs it,
 // and one of them starts the bulk store and hands the stage back once the store has read it.  The two
-// sides only meet at the stages' full / empty mbarriers, so a fix-up never delays the next load.
+// sides only meet at the stages' full / empty mbarriers (empty: one arrival per consumer warp), so a fix-up never
+// delays the next load.
 __global__ void __launch_bounds__(kSsThreads, 6) stream_ops_kernel(const __grid_constant__ SsProgram prog,
                                                                    unsigned long long* __restrict__ counter) {
   extern __shared__ __align__(128) uint8_t ss_smem[];
@@ -184,7 +185,7 @@ __global__ void __launch_bounds__(kSsThreads, 6) stream_ops_kernel(const __grid_
   if (threadIdx.x < prog.nops)
     s_base[threadIdx.x] = prog.ops[threadIdx.x].kind == TXF_OP_FILL_STR ? __ldg(reinterpret_cast<const int32_t*>(prog.ops[threadIdx.x].in0)) : 0;
   if (threadIdx.x == 0) {
-    for (int s = 0; s < kSsStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    for (int s = 0; s < kSsStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], kSsConsumers / 32); }
     mbar_fence_init();
   }
   __syncthreads();
@@ -247,6 +248,7 @@ __global__ void __launch_bounds__(kSsThreads, 6) stream_ops_kernel(const __grid_
     const int s = static_cast<int>(k % kSsStages);
     mbar_wait(&full[s], (k / kSsStages) & 1u);
     const long long desc = s_job[s];
+    __syncwarp();  // every lane has seen this phase of full[s] and read the job before a lane of the warp moves on
     if (desc < 0) break;
     const int o = static_cast<int>(desc & 0xFF);
     const SsOp& op = prog.ops[o];
@@ -257,6 +259,10 @@ __global__ void __launch_bounds__(kSsThreads, 6) stream_ops_kernel(const __grid_
       fence_proxy_async();  // the bulk store reads what the threads just wrote
       consumer_bar(1);
     }
+    // A stage goes back to the producer once EVERY consumer warp is done with it: the elected thread arrives when the
+    // store has read the stage (one iteration later), the other warps' first lanes here -- so no warp can fall a
+    // whole round of stages behind and miss a phase of full[s] (pure-copy tiles have no other meeting point).
+    if (lane == 0 && !elected) mbar_arrive(&empty[s]);
     if (elected) {
       if (!partial) {
         const long long c0 = (desc >> 16) * op.per_tile;
