@@ -520,7 +520,7 @@ __global__ void __launch_bounds__(256) bsel_hist_kernel(const uint32_t* __restri
       lo = lt ? lo + half + 1 : lo;
       len = lt ? len - half - 1 : half;
     }
-    const int p = (lo - 1) >> 1;  // candidates lie strictly inside a bracket: lo is odd
+    const int p = (lo & 1) ? (lo - 1) >> 1 : 0;  // candidates lie strictly inside a bracket: lo is odd
     const uint32_t bin = key - bs_edges[2 * p] - 1u;
     if (!(lo & 1) || bin >= static_cast<uint32_t>(B)) {
       atomicOr(over, 1u);
