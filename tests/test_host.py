@@ -538,3 +538,18 @@ def test_stream_kernel_pipeline_protocol_model():
     assert set(results) == {"ok"}
     old = [m.run(rng.randint(20, 40), 0.0, True, True, rng) for _ in range(200)]
     assert any(r != "ok" for r in old)
+
+
+def test_count_table_insert_protocol_model():
+    """tools/model/count_table_model.py: random interleavings of the global count table's lock-free insert with many
+    terms sharing a (truncated) fingerprint and a home slot -- one slot per distinct term, exact counts; without the
+    byte compare the same schedules merge terms."""
+    import importlib.util
+    import random
+    spec = importlib.util.spec_from_file_location("count_table_model", os.path.join(ROOT, "tools", "model", "count_table_model.py"))
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    rng = random.Random(3)
+    for verify, expect_ok in ((True, True), (False, False)):
+        results = [m.run(rng.randint(2, 8), 64, m.make_terms(rng, rng.randint(4, 14), 2, 4), rng, verify) for _ in range(200)]
+        assert all(r == "ok" for r in results) == expect_ok, results[:5]
