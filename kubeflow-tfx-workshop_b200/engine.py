@@ -418,17 +418,6 @@ class Engine:
             with torch.cuda.stream(sq):
                 pending_q = {nb: self._quantiles_count(nb, pq, chunks) for nb, pq in pending_q.items()}
                 self._mark("quantiles_counted")
-            if self.comm.active and self.comm.world >= self.drain_between_steps_world:
-                # Same rule as for the count pass and the stream kernel, for the same rank counts as the drain in
-                # analyze_and_transform: the moments pass is one resident wave without shared memory.  If it is already on
-                # the SMs when the sample all-gather completes, the count pass's CTAs (which need an IDLE SM to switch its
-                # L1/shared split) cannot start, while the quantile count pass's CTAs fit the split that is there and take
-                # the slots the moments CTAs free -- the count pass would then wait for that whole pass (~1 ms, the size of
-                # the slow-down seen on 4 and 8 ranks).  Queued behind the all-gather it is released together with the
-                # others and, at normal priority, placed after them, as in a step that starts on an idle GPU.
-                for pq in pending_q.values():
-                    if pq.get("gathered") is not None:
-                        main.wait_event(pq["gathered"])
             self._analyze_moments(chunks, state, defer)
             self._analyze_minmax(chunks, state, defer)
             self._mark("moments_done")
