@@ -395,7 +395,10 @@ def run_b200(args):
                    "quantile_path": {str(k): v for k, v in eng.last_quantile_path.items()},
                    "entry_point": "Engine.analyze + Engine.transform" if args.no_overlap else
                                   "Engine.analyze_and_transform (state-free ops streamed under the analyzers)",
-                   "parallelism": f"rows sharded over {world} GPU(s)"},
+                   "parallelism": f"rows sharded over {world} GPU(s)",
+                   "inter_step": ("the host lets a step drain before it queues the next (Engine.drain_between_steps_world)"
+                                  if (comm.active and world >= eng.drain_between_steps_world and not args.no_overlap)
+                                  else "steps queued back to back")},
         "phases_ms": {"analyze_alone": analyze_ms, "transform_alone": transform_ms, "sum_not_overlapped": analyze_ms + transform_ms},
         "roofline": {"bound": "hbm", "kernel": "transform_tiles_kernel", "achieved": xf_gbs, "peak": peak, "unit": "GB/s",
                      "frac": xf_gbs / peak, "traffic": traffic, "peak_source": peak_src,
