@@ -553,3 +553,29 @@ def test_count_table_insert_protocol_model():
     for verify, expect_ok in ((True, True), (False, False)):
         results = [m.run(rng.randint(2, 8), 64, m.make_terms(rng, rng.randint(4, 14), 2, 4), rng, verify) for _ in range(200)]
         assert all(r == "ok" for r in results) == expect_ok, results[:5]
+
+
+def test_unsupported_tft_keywords_raise_at_trace_time(ktw):
+    """Keyword names follow tft 0.13; what this path does not implement raises where tft would be
+    called -- at trace time -- never silently ignored."""
+    tft, g = ktw.tft, ktw.graph
+    s, x = g.Const("a"), g.Const(1.0)
+    for call in (lambda: tft.scale_to_z_score(x, elementwise=True),
+                 lambda: tft.compute_and_apply_vocabulary(s, weights=x),
+                 lambda: tft.compute_and_apply_vocabulary(s, labels=x),
+                 lambda: tft.compute_and_apply_vocabulary(x),              # numeric input
+                 lambda: tft.vocabulary(s, store_frequency=True),
+                 lambda: tft.mean(x, reduce_instance_dims=False),
+                 lambda: tft.scale_to_0_1(x, elementwise=True),
+                 lambda: tft.bucketize(x, 10, weights=x)):
+        with pytest.raises(NotImplementedError):
+            call()
+    for call in (lambda: tft.compute_and_apply_vocabulary(s, num_oov_buckets=-1),
+                 lambda: tft.compute_and_apply_vocabulary(s, top_k=True),
+                 lambda: tft.compute_and_apply_vocabulary(s, frequency_threshold=-2),
+                 lambda: tft.scale_by_min_max(x, 1.0, 1.0)):
+        with pytest.raises(ValueError):
+            call()
+    with pytest.raises(TypeError):
+        tft.bucketize(x, True)
+    assert tft.string_to_int is tft.compute_and_apply_vocabulary and tft.uniques is tft.vocabulary
