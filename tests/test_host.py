@@ -579,3 +579,21 @@ def test_unsupported_tft_keywords_raise_at_trace_time(ktw):
     with pytest.raises(TypeError):
         tft.bucketize(x, True)
     assert tft.string_to_int is tft.compute_and_apply_vocabulary and tft.uniques is tft.vocabulary
+
+
+def test_committed_bench_lines_are_self_consistent():
+    """Every bench.py record under profiles/ recomputes from its own primary fields (tools/check_bench_line.py):
+    value from rows and ms_per_step, roofline fractions from achieved / peak, the end-to-end fraction of the
+    measured host-link ceiling from the bytes copied."""
+    import glob
+    import importlib.util
+    import json
+    spec = importlib.util.spec_from_file_location("check_bench_line", os.path.join(ROOT, "tools", "check_bench_line.py"))
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    paths = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_bench*.json")))
+    assert len(paths) >= 8
+    for p in paths:
+        line = json.loads(open(p).read().strip().splitlines()[-1])
+        assert m.check(line) == [], p
+        assert line.get("parity_check", {"ok": True})["ok"] is True, p
