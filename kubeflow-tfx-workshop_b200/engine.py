@@ -418,6 +418,15 @@ class Engine:
             with torch.cuda.stream(sq):
                 pending_q = {nb: self._quantiles_count(nb, pq, chunks) for nb, pq in pending_q.items()}
                 self._mark("quantiles_counted")
+            if self.comm.active and self.comm.world >= self.drain_between_steps_world:
+                # >= 4 ranks: like the other persistent kernels the moments pass waits for the sample all-gather.  If its
+                # wave of CTAs is on the SMs when the all-gather completes (a rank that waits for slower peers has queued
+                # everything by then), the kernels released there are not placed at once but as SMs drain, in PRIORITY
+                # order -- see the note at the stream kernel's stream.  Released with them it is placed last (normal
+                # priority, no room next to the count pass), as in a step launched kernel by kernel (hypothesis, not measured).
+                for pq in pending_q.values():
+                    if pq.get("gathered") is not None:
+                        main.wait_event(pq["gathered"])
             self._analyze_moments(chunks, state, defer)
             self._analyze_minmax(chunks, state, defer)
             self._mark("moments_done")
@@ -1398,7 +1407,13 @@ class Engine:
                 self._check_table(c)
             main = torch.cuda.current_stream()
             if self._xstream is None:
-                self._xstream = torch.cuda.Stream(device=self.device)
+                # >= 4 ranks: the same priority as the analyzers' streams, so that among the kernels the sample all-gather
+                # releases the launch order decides, as in a step whose kernels are launched one by one on an idle GPU: a CTA
+                # of the quantile count pass (256 threads x 32 registers, 35 KB) FITS the slot next to a count-pass CTA that
+                # the stream kernel's CTA is meant to take, and at a higher priority it would be placed first whenever both
+                # are pending (hypothesis, not measured; with fewer ranks the measured configuration is kept)
+                many = self.comm.active and self.comm.world >= self.drain_between_steps_world
+                self._xstream = torch.cuda.Stream(device=self.device, priority=self._side_priority if many else 0)
             xs = self._xstream
             if self.comm.active and self.comm.world >= self.drain_between_steps_world and self._step_end is not None:
                 # 4 and 8 ranks, measured (profiles/r2_ab_wait_4gpu.txt, r2_exchange_timeline_8gpu_head.txt): a step that starts on
